@@ -1,0 +1,84 @@
+/* Retrieval oracle, C twin of oracle/retrieval_oracle.py -- TEST INFRASTRUCTURE ONLY.
+ *
+ * Same stated rule (see the Python file's header; parity unpinned by the
+ * reference, whose search is a substring test at
+ * pilott/memory/enhanced_memory.py:110):
+ *   bf16 inputs, fp64 accumulation over d = 0..D-1 in order, cosine with
+ *   den = sqrt(nq)*sqrt(nm), score = den > 0 ? dot/den : 0, rank by
+ *   (score desc, insertion sequence asc), filter as enhanced_memory.py:118-131
+ *   and expiry as :20-21.
+ * Built with -ffp-contract=off; the bf16*bf16 products are exact in fp64 so
+ * contraction could not change a bit anyway.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+static inline double bf2d(uint16_t b) {
+    uint32_t u = ((uint32_t)b) << 16;
+    float f;
+    memcpy(&f, &u, 4);
+    return (double)f;
+}
+
+/* scores[q*N + n] for all rows; ld = row stride of m in elements. */
+void oracle_exact_scores(const uint16_t* q, int64_t Q, const uint16_t* m, int64_t N,
+                         int D, int64_t ld_q, int64_t ld_m, double* out) {
+    double* qd = (double*)malloc(sizeof(double) * (size_t)D);
+    for (int64_t qi = 0; qi < Q; ++qi) {
+        double nq = 0.0;
+        for (int d = 0; d < D; ++d) {
+            qd[d] = bf2d(q[qi * ld_q + d]);
+            nq += qd[d] * qd[d];
+        }
+        const double sq = sqrt(nq);
+        for (int64_t n = 0; n < N; ++n) {
+            const uint16_t* row = m + n * ld_m;
+            double dot = 0.0, nm = 0.0;
+            for (int d = 0; d < D; ++d) {
+                const double v = bf2d(row[d]);
+                dot += qd[d] * v;
+                nm += v * v;
+            }
+            const double den = sq * sqrt(nm);
+            out[qi * N + n] = den > 0.0 ? dot / den : 0.0;
+        }
+    }
+    free(qd);
+}
+
+/* (score desc, seq asc): returns 1 when a ranks before b. */
+static inline int before(double sa, int64_t qa, double sb, int64_t qb) {
+    return sa > sb || (sa == sb && qa < qb);
+}
+
+/* Full search over a slot-ordered store.  seq[n] < 0 marks a never-written slot. */
+void oracle_search(const uint16_t* q, int64_t Q, const uint16_t* m, int64_t N, int D,
+                   int64_t ld_q, int64_t ld_m, const int64_t* seq, const int32_t* prio,
+                   const uint64_t* tagmask, const int64_t* expires_us, int32_t min_prio,
+                   uint64_t req_tags, int64_t now_us, int k, int64_t* out_idx,
+                   double* out_score) {
+    double* sc = (double*)malloc(sizeof(double) * (size_t)N);
+    for (int64_t qi = 0; qi < Q; ++qi) {
+        oracle_exact_scores(q + qi * ld_q, 1, m, N, D, ld_q, ld_m, sc);
+        int64_t* bi = out_idx + qi * k;
+        double* bs = out_score + qi * k;
+        int have = 0;
+        for (int j = 0; j < k; ++j) { bi[j] = -1; bs[j] = -INFINITY; }
+        for (int64_t n = 0; n < N; ++n) {
+            if (seq[n] < 0) continue;
+            if (prio[n] < min_prio) continue;
+            if ((tagmask[n] & req_tags) != req_tags) continue;
+            if (expires_us[n] != 0 && now_us > expires_us[n]) continue;
+            if (have == k && !before(sc[n], seq[n], bs[k - 1], bi[k - 1])) continue;
+            int j = have < k ? have : k - 1;
+            while (j > 0 && before(sc[n], seq[n], bs[j - 1], bi[j - 1])) {
+                bs[j] = bs[j - 1]; bi[j] = bi[j - 1]; --j;
+            }
+            bs[j] = sc[n]; bi[j] = seq[n];
+            if (have < k) ++have;
+        }
+    }
+    free(sc);
+}
