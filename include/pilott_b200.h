@@ -1,0 +1,172 @@
+/* pilott_b200.h -- C ABI of the B200-native PilottAI hot path.
+ *
+ * One shared library (libpilott_b200.so), plain pointers and sizes, no torch or
+ * C++ types in any signature.  Every entry point returns 0 on success or a
+ * negative PILOTT_E* code; pilott_last_error() then describes the failure
+ * (thread-local string).  Pointers named *_dev are device pointers on the
+ * store's GPU, *_host are ordinary host pointers.  `stream` is a cudaStream_t
+ * passed as void* (NULL = the legacy default stream).  Calls on one handle must
+ * be serialised by the caller (the reference serialises them with asyncio locks:
+ * pilott/memory/enhanced_memory.py:85,103; pilott/core/router.py:37); different
+ * handles are independent.
+ *
+ * Citations are paths under the reference tree (appyjain21/pilottai).
+ */
+#ifndef PILOTT_B200_H
+#define PILOTT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PILOTT_OK 0
+#define PILOTT_EINVAL (-1)   /* bad argument */
+#define PILOTT_ECUDA (-2)    /* CUDA runtime / driver error */
+#define PILOTT_ENOMEM (-3)   /* device or host allocation failed */
+#define PILOTT_EUNSUPPORTED (-4)
+
+/* Largest k the fused similarity + top-k path answers; larger k (and queries the
+ * fused path flags as not provably exact) go through pilott_mem_search_exact. */
+#define PILOTT_MAX_FUSED_K 32
+/* Tags are stored as one 64-bit mask per row. */
+#define PILOTT_MAX_TAGS 64
+
+typedef struct pilott_mem pilott_mem_t;
+
+const char* pilott_last_error(void);
+int pilott_version(void);
+/* Candidates the fused path keeps per query before the exact re-score (32). */
+int pilott_kp(void);
+
+/* ---- semantic store ----------------------------------------------------------------
+ * Replaces EnhancedMemory.__init__'s bounded deque (pilott/memory/enhanced_memory.py:25-47):
+ * a device-resident ring of `capacity` rows; the oldest row is overwritten when full
+ * (deque(maxlen) semantics, :27,:86).  Per row: bf16[dim] vector (row stride = dim
+ * rounded up to 64), fp32 inverse norm, int32 priority, uint64 tag mask, int64
+ * expires_at in microseconds (0 = never), implicit int64 insertion sequence. */
+int pilott_mem_create(int dim, int64_t capacity, int device, pilott_mem_t** out);
+int pilott_mem_destroy(pilott_mem_t* h);
+/* EnhancedMemory.clear, enhanced_memory.py:284-292 (semantic store part). */
+int pilott_mem_clear(pilott_mem_t* h, void* stream);
+/* total = rows ever appended, count = rows currently held. */
+int pilott_mem_info(const pilott_mem_t* h, int64_t* total, int64_t* count, int64_t* capacity,
+                    int* dim, int* row_stride);
+/* which = 0: scan kernel (0 auto, 1 generic CUDA-core, 2 tcgen05 1-CTA, 3 tcgen05 CTA-pair).
+ * which = 1: CTAs used by the scan (0 = one per SM). */
+int pilott_mem_set_option(pilott_mem_t* h, int which, int64_t value);
+/* Kernel launches enqueued by this handle since creation (bench bookkeeping). */
+int64_t pilott_mem_launch_count(const pilott_mem_t* h);
+
+/* Replaces EnhancedMemory.store_semantic + _update_indexes (enhanced_memory.py:60-91,
+ * :133-144) for a batch of n rows: fp32 -> bf16 (RNE), fused sum of squares -> inverse
+ * norm, metadata columns, ring head advance.  x is [n, dim] fp32 row-major.  prio /
+ * tagmask / expires_us may be NULL (zeros).  *first_seq receives the insertion
+ * sequence number of row 0 (host int64, may be NULL).  n must be <= capacity. */
+int pilott_mem_append(pilott_mem_t* h, const float* x_dev, int64_t n, const int32_t* prio_dev,
+                      const uint64_t* tagmask_dev, const int64_t* expires_us_dev,
+                      int64_t* first_seq, void* stream);
+/* Same with host buffers: stages through pinned memory on the handle's own stream and
+ * returns after the rows are resident. */
+int pilott_mem_append_host(pilott_mem_t* h, const float* x_host, int64_t n,
+                           const int32_t* prio_host, const uint64_t* tagmask_host,
+                           const int64_t* expires_us_host, int64_t* first_seq);
+
+/* Replaces EnhancedMemory.semantic_search + _get_candidate_indexes + MemoryItem.is_expired
+ * (enhanced_memory.py:93-131, :20-21) for a batch of nq queries, with cosine similarity in
+ * place of the reference's substring test (:110):
+ *   candidates: priority >= min_prio AND (tagmask & req_tagmask) == req_tagmask
+ *               AND NOT (expires_us != 0 AND now_us > expires_us)
+ *   score:      cosine over bf16-rounded inputs (exact fp64 re-score of the survivors of
+ *               the tensor-core pass, accumulated d = 0..dim-1 in order)
+ *   rank:       (score desc, insertion sequence asc); k results per query.
+ * q is [nq, dim] fp32.  out_idx [nq,k] receives insertion sequence numbers (-1 = fewer than
+ * k candidates), out_score [nq,k] fp32 (-inf padding), out_score64 [nq,k] fp64 may be NULL.
+ * *out_inexact_dev (device int32, may be NULL) receives how many queries could NOT be
+ * proven exact (their gap check failed) and out_flags_dev [nq] (uint8, may be NULL) marks
+ * them; re-run those through pilott_mem_search_exact.  1 <= k <= PILOTT_MAX_FUSED_K. */
+int pilott_mem_search(pilott_mem_t* h, const float* q_dev, int64_t nq, int k, int32_t min_prio,
+                      uint64_t req_tagmask, int64_t now_us, int64_t* out_idx_dev,
+                      float* out_score_dev, double* out_score64_dev, int32_t* out_inexact_dev,
+                      uint8_t* out_flags_dev, void* stream);
+/* Host-buffer variant: H2D of the queries, the search, the exact fallback for flagged
+ * queries (and for k > PILOTT_MAX_FUSED_K), D2H of the results; synchronous.
+ * *n_fallback (may be NULL) = queries that went through the exact path. */
+int pilott_mem_search_host(pilott_mem_t* h, const float* q_host, int64_t nq, int k,
+                           int32_t min_prio, uint64_t req_tagmask, int64_t now_us,
+                           int64_t* out_idx_host, float* out_score_host, double* out_score64_host,
+                           int32_t* n_fallback);
+/* Brute-force fp64 search (any k >= 1): every candidate row scored in the oracle's order.
+ * Slow path for flagged queries / large k.  query_ids_dev (int32[nsel], may be NULL = all
+ * nq) selects which rows of q/out to process. */
+int pilott_mem_search_exact(pilott_mem_t* h, const float* q_dev, int64_t nq, const int32_t* query_ids_dev,
+                            int64_t nsel, int k, int32_t min_prio, uint64_t req_tagmask,
+                            int64_t now_us, int64_t* out_idx_dev, float* out_score_dev,
+                            double* out_score64_dev, void* stream);
+
+/* Replaces EnhancedMemory.cleanup's semantic-store pass (enhanced_memory.py:258-272):
+ * drops expired rows and rebuilds the ring densely in insertion order.  `total` is
+ * unchanged; the i-th oldest survivor is renumbered total - kept + i (the reference
+ * renumbers positions the same way when it rebuilds its indexes, :270-272).
+ * *kept (host, may be NULL) = rows surviving.
+ * keep_host (uint8[count], may be NULL) receives the keep flag of every held row in age
+ * order so the host can drop the same MemoryItems.  Synchronous. */
+int pilott_mem_compact(pilott_mem_t* h, int64_t now_us, int64_t* kept, uint8_t* keep_host);
+
+/* Read back raw columns of the held rows in age order (tests, snapshots). Any pointer may
+ * be NULL.  vec_bits_host is [count, dim] uint16 bf16 bit patterns. Synchronous. */
+int pilott_mem_export(pilott_mem_t* h, uint16_t* vec_bits_host, float* inv_norm_host,
+                      int32_t* prio_host, uint64_t* tagmask_host, int64_t* expires_us_host);
+
+/* ---- multi-GPU merge ---------------------------------------------------------------
+ * After an all-gather of per-shard results: idx/score64 are [n_shards, nq, k]; picks the
+ * global top-k per query by (score desc, idx asc).  No reference counterpart: the reference
+ * is single-process; this is the exchange step of the row-sharded
+ * store. */
+int pilott_topk_merge(const int64_t* idx_dev, const double* score64_dev, int n_shards, int64_t nq,
+                      int k, int64_t* out_idx_dev, float* out_score_dev, double* out_score64_dev,
+                      void* stream);
+
+/* ---- routing -----------------------------------------------------------------------
+ * One call scores nt tasks against na agents and returns, per task, the first agent with
+ * the maximal score among the viable ones (-1 = none) -- the inner loops of
+ *   TaskRouter._calculate_agent_scores + _attempt_routing   pilott/core/router.py:51-95
+ *   LoadBalancer._find_best_agent + _calculate_agent_suitability
+ *                                         pilott/orchestration/load_balancer.py:268-336
+ *   TaskDelegator._find_best_agent + _calculate_total_score
+ *                                         pilott/delegation/task_delegator.py:60-113
+ * with BaseAgent.evaluate_task_suitability (pilott/core/agent.py:549-575) folded in.
+ * The per-agent fp64 terms are precomputed by the host in the reference's own operation
+ * order (see pilottai_b200/routing.py); the device does the task x agent matching and the
+ * remaining fp64 additions with one rounding each, so scores are bit-identical to Python.
+ *
+ * words:            64-bit words per capability / specialization bit set (vocab <= 64*words)
+ * task_req [nt,words]   required capabilities          task_tags [nt,words] task tags
+ * task_type [nt]        specialization id of task.get('type','') (-1 = not in the vocabulary)
+ * task_flags [nt]       bit0: 'required_capabilities' key present, bit1: 'type' key present
+ * agent_caps/agent_spec [na,words]; agent_flags [na]: bit0 viable, bit1 has required-caps
+ *                       attribute, bit2 has specializations
+ * agent_s12 [na,3]      first two score terms for base in {missing-cap, no type match, type match}
+ * agent_t4 [na]         last score term
+ * spec_u [2][max_tags+1] router spec*0.2, indexed [type match][tag matches]; max_tags >= 64*words
+ * mode: 0 router (s12 + u + t4), 1 load balancer / 2 delegator (s12 holds the full score;
+ *       mode 2 additionally requires score > 0).
+ * out_agent [nt] int32, out_score [nt] fp64 (NaN when no agent). */
+int pilott_route_score(const uint64_t* task_req_dev, const uint64_t* task_tags_dev,
+                       const int32_t* task_type_dev, const uint8_t* task_flags_dev, int64_t nt,
+                       const uint64_t* agent_caps_dev,
+                       const uint64_t* agent_spec_dev, const uint8_t* agent_flags_dev,
+                       const double* agent_s12_dev, const double* agent_t4_dev, int na, int words,
+                       const double* spec_u_dev, int max_tags, int mode, int32_t* out_agent_dev,
+                       double* out_score_dev, void* stream);
+
+/* TaskRouter.get_task_priority (pilott/core/router.py:135-145) for nt tasks:
+ * 3 critical, 2 high, 1 medium, 0 low. */
+int pilott_task_priority(const uint8_t* urgent_dev, const int32_t* complexity_dev,
+                         const int32_t* n_deps_dev, int64_t nt, uint8_t* out_dev, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PILOTT_B200_H */

@@ -1,0 +1,604 @@
+// abi.cu -- the extern "C" surface declared in include/pilott_b200.h: handle management,
+// argument checking, scratch sizing, tensor-map encoding and kernel sequencing.
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cudaTypedefs.h>
+
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/pilott_b200.h"
+#include "internal.h"
+
+namespace {
+
+constexpr int KP_HOST = 32;   // == pilott::KP in common.cuh
+thread_local std::string g_err;
+
+int fail(int code, const std::string& msg) {
+    g_err = msg;
+    return code;
+}
+int fail_cuda(cudaError_t e, const char* what) {
+    g_err = std::string(what) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")";
+    return e == cudaErrorMemoryAllocation ? PILOTT_ENOMEM : PILOTT_ECUDA;
+}
+#define CK(expr)                                                   \
+    do {                                                           \
+        cudaError_t _e = (expr);                                   \
+        if (_e != cudaSuccess) return fail_cuda(_e, #expr);        \
+    } while (0)
+
+PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
+
+int get_encode() {
+    if (g_encode) return PILOTT_OK;
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || fn == nullptr)
+        return fail(PILOTT_ECUDA, "cuTensorMapEncodeTiled is not available from the driver");
+    g_encode = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(fn);
+    return PILOTT_OK;
+}
+
+// 2-D bf16 tensor [rows, ld] (ld contiguous), box = 64 x box_rows, 128-byte swizzle.
+int encode_map(CUtensorMap* map, const void* ptr, int64_t rows, int ld, int box_rows) {
+    int rc = get_encode();
+    if (rc) return rc;
+    cuuint64_t gdim[2] = {(cuuint64_t)ld, (cuuint64_t)(rows > 0 ? rows : 1)};
+    cuuint64_t gstride[1] = {(cuuint64_t)ld * 2};
+    cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride,
+                          box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(PILOTT_ECUDA, "cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
+    return PILOTT_OK;
+}
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    int ensure(size_t need) {
+        if (need <= bytes) return PILOTT_OK;
+        if (p) cudaFree(p);
+        p = nullptr; bytes = 0;
+        size_t want = need + need / 4;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) { p = nullptr; return fail_cuda(e, "cudaMalloc(scratch)"); }
+        bytes = want;
+        return PILOTT_OK;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+};
+struct HostBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    int ensure(size_t need) {
+        if (need <= bytes) return PILOTT_OK;
+        if (p) cudaFreeHost(p);
+        p = nullptr; bytes = 0;
+        cudaError_t e = cudaMallocHost(&p, need + need / 4);
+        if (e != cudaSuccess) { p = nullptr; return fail_cuda(e, "cudaMallocHost(staging)"); }
+        bytes = need + need / 4;
+        return PILOTT_OK;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; bytes = 0; }
+};
+
+bool is_pinned(const void* p) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return at.type == cudaMemoryTypeHost;
+}
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+}  // namespace
+
+struct pilott_mem {
+    int dim = 0, ld = 0, device = 0, num_sms = 0;
+    int64_t capacity = 0, cap_pad = 0;
+    int64_t total = 0;      // rows ever appended (sequence numbering)
+    int64_t count = 0;      // rows held
+    int64_t head = 0;       // physical slot of the oldest row
+    void* vec = nullptr;
+    float* inv_norm = nullptr;
+    int32_t* prio = nullptr;
+    uint64_t* tagmask = nullptr;
+    int64_t* expires = nullptr;
+    float* scale = nullptr;
+    DevBuf qbuf, partials, exact_scratch, stage_dev, result_dev, misc_dev;
+    HostBuf stage_host;
+    cudaStream_t own_stream = nullptr;
+    CUtensorMap map_c;
+    bool tc_ok = false;
+    int opt_kernel = 0;     // 0 auto, 1 generic, 2 tc 1-CTA, 3 tc pair
+    int opt_ctas = 0;
+    int64_t launches = 0;
+};
+
+namespace {
+
+int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
+
+void free_columns(pilott_mem* h) {
+    cudaFree(h->vec); cudaFree(h->inv_norm); cudaFree(h->prio); cudaFree(h->tagmask);
+    cudaFree(h->expires); cudaFree(h->scale);
+    h->vec = nullptr; h->inv_norm = nullptr; h->prio = nullptr; h->tagmask = nullptr;
+    h->expires = nullptr; h->scale = nullptr;
+}
+
+int alloc_columns(pilott_mem* h) {
+    const size_t n = (size_t)h->capacity;
+    CK(cudaMalloc(&h->vec, n * h->ld * 2));
+    CK(cudaMalloc(&h->inv_norm, n * 4));
+    CK(cudaMalloc(&h->prio, n * 4));
+    CK(cudaMalloc(&h->tagmask, n * 8));
+    CK(cudaMalloc(&h->expires, n * 8));
+    CK(cudaMalloc(&h->scale, (size_t)h->cap_pad * 4));
+    CK(cudaMemset(h->vec, 0, n * h->ld * 2));
+    CK(cudaMemset(h->inv_norm, 0, n * 4));
+    CK(cudaMemset(h->prio, 0, n * 4));
+    CK(cudaMemset(h->tagmask, 0, n * 8));
+    CK(cudaMemset(h->expires, 0, n * 8));
+    h->tc_ok = false;
+    if (encode_map(&h->map_c, h->vec, h->capacity, h->ld, 256) == PILOTT_OK) {
+        // the pair kernel loads 128-row halves; a second map would only differ in the box, so
+        // the box is chosen per launch below (see search_core).
+        h->tc_ok = true;
+    }
+    return PILOTT_OK;
+}
+
+// Chooses the scan kernel: 1 generic, 2 tcgen05 1-CTA, 3 tcgen05 CTA pair.
+int pick_kernel(const pilott_mem* h) {
+    if (h->opt_kernel == 1) return 1;
+    if (!h->tc_ok) return 1;
+    if (h->opt_kernel == 2 || h->opt_kernel == 3) return h->opt_kernel;
+    return 2;
+}
+
+int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t min_prio, uint64_t req,
+                int64_t now_us, int64_t* out_idx, float* out_score, double* out_score64,
+                int32_t* out_inexact, uint8_t* out_flags, cudaStream_t st) {
+    if (nq <= 0) return PILOTT_OK;
+    if (k < 1 || k > PILOTT_MAX_FUSED_K) return fail(PILOTT_EINVAL, "k must be in [1, 32] for the fused path");
+    const int64_t nq_pad = round_up(nq, 256);
+    int rc = h->qbuf.ensure((size_t)nq_pad * h->ld * 2);
+    if (rc) return rc;
+    CK(pilott::launch_convert_queries(q_dev, nq, h->dim, h->ld, h->qbuf.p, st));
+    CK(pilott::launch_scale(h->inv_norm, h->prio, h->tagmask, h->expires, h->count, h->cap_pad,
+                            min_prio, req, now_us, h->scale, st));
+    h->launches += 2;
+
+    int kern = pick_kernel(h);
+    const int ctas = h->opt_ctas > 0 ? h->opt_ctas : h->num_sms;
+    pilott::ScanArgs a{};
+    a.qb = h->qbuf.p; a.vec = h->vec; a.scale = h->scale; a.nq = nq;
+    a.nslots = h->count; a.capacity = h->capacity; a.head = h->head; a.ld = h->ld;
+    CUtensorMap map_q, map_c;
+    if (kern != 1) {
+        const int cg = kern == 3 ? 2 : 1;
+        rc = encode_map(&map_q, h->qbuf.p, nq, h->ld, 128);
+        if (rc) return rc;
+        if (cg == 1) map_c = h->map_c;
+        else { rc = encode_map(&map_c, h->vec, h->capacity, h->ld, 128); if (rc) return rc; }
+        a.slots = pilott::scan_tc_slots(nq, h->count, cg, ctas);
+        rc = h->partials.ensure((size_t)nq * a.slots * KP_HOST * 8);
+        if (rc) return rc;
+        a.partials = (uint64_t*)h->partials.p;
+        CK(pilott::launch_scan_tc(a, &map_q, &map_c, cg, ctas, st));
+    } else {
+        a.slots = pilott::scan_generic_slots(nq, h->count, h->num_sms);
+        rc = h->partials.ensure((size_t)nq * a.slots * KP_HOST * 8);
+        if (rc) return rc;
+        a.partials = (uint64_t*)h->partials.p;
+        CK(pilott::launch_scan_generic(a, h->num_sms, st));
+    }
+    if (out_inexact) CK(cudaMemsetAsync(out_inexact, 0, 4, st));
+    pilott::FinishArgs f{};
+    f.partials = a.partials; f.slots = a.slots; f.qb = h->qbuf.p; f.vec = h->vec; f.ld = h->ld;
+    f.nq = nq; f.capacity = h->capacity; f.head = h->head; f.base_seq = h->total - h->count;
+    f.k = k;
+    f.err = h->ld * 2.4e-7 > 1e-4 ? h->ld * 2.4e-7 : 1e-4;
+    f.out_idx = out_idx; f.out_score = out_score; f.out_score64 = out_score64;
+    f.flags = out_flags; f.inexact = out_inexact;
+    CK(pilott::launch_finish(f, st));
+    h->launches += 2;
+    return PILOTT_OK;
+}
+
+int exact_core(pilott_mem* h, const float* q_dev, int64_t nq, const int32_t* qids, int64_t nsel, int k,
+               int32_t min_prio, uint64_t req, int64_t now_us, int64_t* out_idx, float* out_score,
+               double* out_score64, cudaStream_t st) {
+    if (nq <= 0) return PILOTT_OK;
+    if (k < 1) return fail(PILOTT_EINVAL, "k must be >= 1");
+    if (!qids) nsel = nq;
+    if (nsel <= 0) return PILOTT_OK;
+    int rc = h->qbuf.ensure((size_t)round_up(nq, 256) * h->ld * 2);
+    if (rc) return rc;
+    CK(pilott::launch_convert_queries(q_dev, nq, h->dim, h->ld, h->qbuf.p, st));
+    h->launches += 1;
+    const int64_t rows = h->count > 0 ? h->count : 1;
+    int64_t chunk = (256ll << 20) / (rows * 8);
+    if (chunk < 1) chunk = 1;
+    if (chunk > nsel) chunk = nsel;
+    if (chunk > 65535) chunk = 65535;
+    rc = h->exact_scratch.ensure((size_t)chunk * rows * 8);
+    if (rc) return rc;
+    std::vector<int32_t> ids;
+    const int32_t* ids_dev = qids;
+    if (!qids) {
+        ids.resize(nsel);
+        for (int64_t i = 0; i < nsel; ++i) ids[i] = (int32_t)i;
+        rc = h->misc_dev.ensure((size_t)nsel * 4);
+        if (rc) return rc;
+        CK(cudaMemcpyAsync(h->misc_dev.p, ids.data(), (size_t)nsel * 4, cudaMemcpyHostToDevice, st));
+        CK(cudaStreamSynchronize(st));      // ids is a stack-lifetime pageable buffer
+        ids_dev = (const int32_t*)h->misc_dev.p;
+    }
+    for (int64_t lo = 0; lo < nsel; lo += chunk) {
+        const int64_t n = nsel - lo < chunk ? nsel - lo : chunk;
+        CK(pilott::launch_exact(h->qbuf.p, h->vec, h->ld, h->prio, h->tagmask, h->expires, h->count,
+                                h->capacity, h->head, h->total - h->count, ids_dev + lo, n, k, min_prio,
+                                req, now_us, (double*)h->exact_scratch.p, out_idx, out_score,
+                                out_score64, st));
+        h->launches += 2;
+    }
+    return PILOTT_OK;
+}
+
+}  // namespace
+
+extern "C" int pilott_kp(void) { return 32; }
+
+extern "C" {
+
+const char* pilott_last_error(void) { return g_err.c_str(); }
+int pilott_version(void) { return 100; }
+
+int pilott_mem_create(int dim, int64_t capacity, int device, pilott_mem_t** out) {
+    if (!out) return fail(PILOTT_EINVAL, "out is NULL");
+    *out = nullptr;
+    if (dim < 1 || dim > 16384) return fail(PILOTT_EINVAL, "dim must be in [1, 16384]");
+    if (capacity < 1 || capacity > 0x7fffff00ll) return fail(PILOTT_EINVAL, "capacity must be in [1, 2^31)");
+    int ndev = 0;
+    CK(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return fail(PILOTT_EINVAL, "no such CUDA device");
+    DeviceGuard g(device);
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) return fail(PILOTT_EUNSUPPORTED, "pilott_b200 kernels are built for sm_100a only");
+    pilott_mem* h = new (std::nothrow) pilott_mem();
+    if (!h) return fail(PILOTT_ENOMEM, "host allocation failed");
+    h->dim = dim; h->ld = (int)round_up(dim, 64); h->device = device; h->num_sms = prop.multiProcessorCount;
+    h->capacity = capacity; h->cap_pad = round_up(capacity, 256) + 256;
+    int rc = alloc_columns(h);
+    if (rc == PILOTT_OK) {
+        cudaError_t e = cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking);
+        if (e != cudaSuccess) rc = fail_cuda(e, "cudaStreamCreate");
+    }
+    if (rc == PILOTT_OK && h->tc_ok) {
+        cudaError_t e = pilott::scan_tc_init();
+        if (e != cudaSuccess) { h->tc_ok = false; cudaGetLastError(); }
+    }
+    if (rc != PILOTT_OK) { free_columns(h); delete h; return rc; }
+    CK(cudaDeviceSynchronize());
+    *out = h;
+    return PILOTT_OK;
+}
+
+int pilott_mem_destroy(pilott_mem_t* h) {
+    if (!h) return PILOTT_OK;
+    DeviceGuard g(h->device);
+    cudaDeviceSynchronize();
+    free_columns(h);
+    h->qbuf.release(); h->partials.release(); h->exact_scratch.release(); h->stage_dev.release();
+    h->result_dev.release(); h->misc_dev.release(); h->stage_host.release();
+    if (h->own_stream) cudaStreamDestroy(h->own_stream);
+    delete h;
+    return PILOTT_OK;
+}
+
+int pilott_mem_clear(pilott_mem_t* h, void* stream) {
+    if (!h) return fail(PILOTT_EINVAL, "handle is NULL");
+    (void)stream;
+    h->total = 0; h->count = 0; h->head = 0;
+    return PILOTT_OK;
+}
+
+int pilott_mem_info(const pilott_mem_t* h, int64_t* total, int64_t* count, int64_t* capacity, int* dim,
+                    int* row_stride) {
+    if (!h) return fail(PILOTT_EINVAL, "handle is NULL");
+    if (total) *total = h->total;
+    if (count) *count = h->count;
+    if (capacity) *capacity = h->capacity;
+    if (dim) *dim = h->dim;
+    if (row_stride) *row_stride = h->ld;
+    return PILOTT_OK;
+}
+
+int pilott_mem_set_option(pilott_mem_t* h, int which, int64_t value) {
+    if (!h) return fail(PILOTT_EINVAL, "handle is NULL");
+    if (which == 0) {
+        if (value < 0 || value > 3) return fail(PILOTT_EINVAL, "scan kernel must be 0..3");
+        if (value >= 2 && !h->tc_ok) return fail(PILOTT_EUNSUPPORTED, "tensor-map encoding unavailable: tcgen05 path disabled");
+        h->opt_kernel = (int)value;
+    } else if (which == 1) {
+        if (value < 0 || value > 4096) return fail(PILOTT_EINVAL, "CTA count out of range");
+        h->opt_ctas = (int)value;
+    } else {
+        return fail(PILOTT_EINVAL, "unknown option");
+    }
+    return PILOTT_OK;
+}
+
+int64_t pilott_mem_launch_count(const pilott_mem_t* h) { return h ? h->launches : 0; }
+
+int pilott_mem_append(pilott_mem_t* h, const float* x_dev, int64_t n, const int32_t* prio_dev,
+                      const uint64_t* tagmask_dev, const int64_t* expires_us_dev, int64_t* first_seq,
+                      void* stream) {
+    if (!h) return fail(PILOTT_EINVAL, "handle is NULL");
+    if (n < 0 || n > h->capacity) return fail(PILOTT_EINVAL, "append batch must hold between 0 and capacity rows");
+    if (first_seq) *first_seq = h->total;
+    if (n == 0) return PILOTT_OK;
+    if (!x_dev) return fail(PILOTT_EINVAL, "x is NULL");
+    DeviceGuard g(h->device);
+    int64_t first_slot = h->head + h->count;
+    if (first_slot >= h->capacity) first_slot -= h->capacity;
+    CK(pilott::launch_append(x_dev, n, h->dim, h->ld, h->vec, h->inv_norm, h->prio, h->tagmask, h->expires,
+                             prio_dev, tagmask_dev, expires_us_dev, first_slot, h->capacity,
+                             (cudaStream_t)stream));
+    h->launches += 1;
+    // ring bookkeeping: deque(maxlen) drops the oldest rows (enhanced_memory.py:27,86)
+    const int64_t over = h->count + n - h->capacity;
+    if (over > 0) { h->head = (h->head + over) % h->capacity; h->count = h->capacity; }
+    else h->count += n;
+    h->total += n;
+    return PILOTT_OK;
+}
+
+int pilott_mem_append_host(pilott_mem_t* h, const float* x_host, int64_t n, const int32_t* prio_host,
+                           const uint64_t* tagmask_host, const int64_t* expires_us_host,
+                           int64_t* first_seq) {
+    if (!h) return fail(PILOTT_EINVAL, "handle is NULL");
+    if (n < 0 || n > h->capacity) return fail(PILOTT_EINVAL, "append batch must hold between 0 and capacity rows");
+    if (n == 0) { if (first_seq) *first_seq = h->total; return PILOTT_OK; }
+    if (!x_host) return fail(PILOTT_EINVAL, "x is NULL");
+    DeviceGuard g(h->device);
+    const size_t xb = (size_t)n * h->dim * 4, pb = (size_t)n * 4, tb = (size_t)n * 8, eb = (size_t)n * 8;
+    const size_t off_p = round_up(xb, 256), off_t = off_p + round_up(pb, 256), off_e = off_t + round_up(tb, 256);
+    const size_t tot = off_e + round_up(eb, 256);
+    int rc = h->stage_host.ensure(tot);
+    if (rc) return rc;
+    rc = h->stage_dev.ensure(tot);
+    if (rc) return rc;
+    char* hs = (char*)h->stage_host.p;
+    char* ds = (char*)h->stage_dev.p;
+    memcpy(hs, x_host, xb);
+    if (prio_host) memcpy(hs + off_p, prio_host, pb);
+    if (tagmask_host) memcpy(hs + off_t, tagmask_host, tb);
+    if (expires_us_host) memcpy(hs + off_e, expires_us_host, eb);
+    cudaStream_t st = h->own_stream;
+    CK(cudaMemcpyAsync(ds, hs, tot, cudaMemcpyHostToDevice, st));
+    rc = pilott_mem_append(h, (const float*)ds, n, prio_host ? (const int32_t*)(ds + off_p) : nullptr,
+                           tagmask_host ? (const uint64_t*)(ds + off_t) : nullptr,
+                           expires_us_host ? (const int64_t*)(ds + off_e) : nullptr, first_seq, st);
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(st));
+    return PILOTT_OK;
+}
+
+int pilott_mem_search(pilott_mem_t* h, const float* q_dev, int64_t nq, int k, int32_t min_prio,
+                      uint64_t req_tagmask, int64_t now_us, int64_t* out_idx_dev, float* out_score_dev,
+                      double* out_score64_dev, int32_t* out_inexact_dev, uint8_t* out_flags_dev,
+                      void* stream) {
+    if (!h) return fail(PILOTT_EINVAL, "handle is NULL");
+    if (nq < 0) return fail(PILOTT_EINVAL, "nq is negative");
+    if (nq > 0 && (!q_dev || !out_idx_dev || !out_score_dev)) return fail(PILOTT_EINVAL, "NULL query or output pointer");
+    DeviceGuard g(h->device);
+    return search_core(h, q_dev, nq, k, min_prio, req_tagmask, now_us, out_idx_dev, out_score_dev,
+                       out_score64_dev, out_inexact_dev, out_flags_dev, (cudaStream_t)stream);
+}
+
+int pilott_mem_search_exact(pilott_mem_t* h, const float* q_dev, int64_t nq, const int32_t* query_ids_dev,
+                            int64_t nsel, int k, int32_t min_prio, uint64_t req_tagmask, int64_t now_us,
+                            int64_t* out_idx_dev, float* out_score_dev, double* out_score64_dev,
+                            void* stream) {
+    if (!h) return fail(PILOTT_EINVAL, "handle is NULL");
+    if (nq < 0) return fail(PILOTT_EINVAL, "nq is negative");
+    if (nq > 0 && (!q_dev || !out_idx_dev || !out_score_dev)) return fail(PILOTT_EINVAL, "NULL query or output pointer");
+    DeviceGuard g(h->device);
+    return exact_core(h, q_dev, nq, query_ids_dev, nsel, k, min_prio, req_tagmask, now_us, out_idx_dev,
+                      out_score_dev, out_score64_dev, (cudaStream_t)stream);
+}
+
+int pilott_mem_search_host(pilott_mem_t* h, const float* q_host, int64_t nq, int k, int32_t min_prio,
+                           uint64_t req_tagmask, int64_t now_us, int64_t* out_idx_host,
+                           float* out_score_host, double* out_score64_host, int32_t* n_fallback) {
+    if (!h) return fail(PILOTT_EINVAL, "handle is NULL");
+    if (n_fallback) *n_fallback = 0;
+    if (nq < 0) return fail(PILOTT_EINVAL, "nq is negative");
+    if (nq == 0) return PILOTT_OK;
+    if (k < 1) return fail(PILOTT_EINVAL, "k must be >= 1");
+    if (!q_host || !out_idx_host || !out_score_host) return fail(PILOTT_EINVAL, "NULL query or output pointer");
+    DeviceGuard g(h->device);
+    cudaStream_t st = h->own_stream;
+    const size_t qb = (size_t)nq * h->dim * 4;
+    // result block: idx | score64 | score | flags | inexact
+    const size_t ib = (size_t)nq * k * 8, s64b = ib, sb = (size_t)nq * k * 4, fb = round_up(nq, 8);
+    const size_t off_s64 = ib, off_s = off_s64 + s64b, off_f = off_s + round_up(sb, 8), off_c = off_f + fb;
+    const size_t rtot = off_c + 8;
+    int rc = h->stage_host.ensure(qb > rtot ? qb : rtot);
+    if (rc) return rc;
+    rc = h->stage_dev.ensure(qb);
+    if (rc) return rc;
+    rc = h->result_dev.ensure(rtot);
+    if (rc) return rc;
+    if (is_pinned(q_host)) {          // caller's buffer is page-locked: DMA straight from it
+        CK(cudaMemcpyAsync(h->stage_dev.p, q_host, qb, cudaMemcpyHostToDevice, st));
+    } else {
+        memcpy(h->stage_host.p, q_host, qb);
+        CK(cudaMemcpyAsync(h->stage_dev.p, h->stage_host.p, qb, cudaMemcpyHostToDevice, st));
+    }
+    char* rd = (char*)h->result_dev.p;
+    const float* qd = (const float*)h->stage_dev.p;
+    int64_t* d_idx = (int64_t*)rd;
+    double* d_s64 = (double*)(rd + off_s64);
+    float* d_s = (float*)(rd + off_s);
+    uint8_t* d_f = (uint8_t*)(rd + off_f);
+    int32_t* d_c = (int32_t*)(rd + off_c);
+    const bool fused = k <= PILOTT_MAX_FUSED_K;
+    if (fused) {
+        rc = search_core(h, qd, nq, k, min_prio, req_tagmask, now_us, d_idx, d_s, d_s64, d_c, d_f, st);
+    } else {
+        rc = exact_core(h, qd, nq, nullptr, nq, k, min_prio, req_tagmask, now_us, d_idx, d_s, d_s64, st);
+        if (n_fallback) *n_fallback = (int32_t)nq;
+    }
+    if (rc) return rc;
+    char* rh = (char*)h->stage_host.p;
+    CK(cudaMemcpyAsync(rh, rd, rtot, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (fused && *(int32_t*)(rh + off_c) > 0) {
+        // exact fallback for the queries whose gap check failed
+        std::vector<int32_t> ids;
+        for (int64_t i = 0; i < nq; ++i) if (((uint8_t*)(rh + off_f))[i]) ids.push_back((int32_t)i);
+        rc = h->misc_dev.ensure(ids.size() * 4);
+        if (rc) return rc;
+        CK(cudaMemcpyAsync(h->misc_dev.p, ids.data(), ids.size() * 4, cudaMemcpyHostToDevice, st));
+        CK(cudaStreamSynchronize(st));
+        rc = exact_core(h, qd, nq, (const int32_t*)h->misc_dev.p, (int64_t)ids.size(), k, min_prio, req_tagmask,
+                        now_us, d_idx, d_s, d_s64, st);
+        if (rc) return rc;
+        CK(cudaMemcpyAsync(rh, rd, rtot, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        if (n_fallback) *n_fallback = (int32_t)ids.size();
+    }
+    memcpy(out_idx_host, rh, ib);
+    memcpy(out_score_host, rh + off_s, sb);
+    if (out_score64_host) memcpy(out_score64_host, rh + off_s64, s64b);
+    return PILOTT_OK;
+}
+
+int pilott_mem_compact(pilott_mem_t* h, int64_t now_us, int64_t* kept, uint8_t* keep_host) {
+    if (!h) return fail(PILOTT_EINVAL, "handle is NULL");
+    DeviceGuard g(h->device);
+    cudaStream_t st = h->own_stream;
+    const int64_t n = h->count;
+    if (kept) *kept = n;
+    if (n == 0) return PILOTT_OK;
+    CK(cudaDeviceSynchronize());
+    int rc = h->misc_dev.ensure((size_t)n);
+    if (rc) return rc;
+    CK(pilott::launch_compact_flags(h->expires, n, h->head, h->capacity, now_us, (uint8_t*)h->misc_dev.p, st));
+    std::vector<uint8_t> keep((size_t)n);
+    CK(cudaMemcpyAsync(keep.data(), h->misc_dev.p, (size_t)n, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    std::vector<int64_t> src;
+    src.reserve((size_t)n);
+    for (int64_t i = 0; i < n; ++i) if (keep[i]) src.push_back((h->head + i) % h->capacity);
+    if (keep_host) memcpy(keep_host, keep.data(), (size_t)n);
+    const int64_t m = (int64_t)src.size();
+    if (kept) *kept = m;
+    h->launches += 1;
+    if (m == n) return PILOTT_OK;
+    // gather the survivors into fresh columns, then swap
+    pilott_mem old = *h;
+    h->vec = nullptr; h->inv_norm = nullptr; h->prio = nullptr; h->tagmask = nullptr;
+    h->expires = nullptr; h->scale = nullptr;
+    rc = alloc_columns(h);
+    if (rc) { free_columns(h); *h = old; return rc; }
+    if (m > 0) {
+        rc = h->stage_dev.ensure((size_t)m * 8);
+        if (rc) return rc;
+        CK(cudaMemcpyAsync(h->stage_dev.p, src.data(), (size_t)m * 8, cudaMemcpyHostToDevice, st));
+        CK(pilott::launch_gather_rows(old.vec, old.inv_norm, old.prio, old.tagmask, old.expires, h->ld,
+                                      (const int64_t*)h->stage_dev.p, m, h->vec, h->inv_norm, h->prio,
+                                      h->tagmask, h->expires, st));
+        h->launches += 1;
+    }
+    CK(cudaStreamSynchronize(st));
+    free_columns(&old);
+    h->head = 0; h->count = m;       // total is unchanged: survivors are re-based to total-m+age
+    return PILOTT_OK;
+}
+
+int pilott_mem_export(pilott_mem_t* h, uint16_t* vec_bits_host, float* inv_norm_host, int32_t* prio_host,
+                      uint64_t* tagmask_host, int64_t* expires_us_host) {
+    if (!h) return fail(PILOTT_EINVAL, "handle is NULL");
+    DeviceGuard g(h->device);
+    CK(cudaDeviceSynchronize());
+    const int64_t n = h->count;
+    // two contiguous physical runs in age order: [head, min(head+n, cap)) then [0, rest)
+    const int64_t run1 = (h->head + n <= h->capacity) ? n : h->capacity - h->head;
+    const int64_t run2 = n - run1;
+    if (vec_bits_host) {
+        CK(cudaMemcpy2D(vec_bits_host, (size_t)h->dim * 2, (const char*)h->vec + (size_t)h->head * h->ld * 2,
+                        (size_t)h->ld * 2, (size_t)h->dim * 2, (size_t)run1, cudaMemcpyDeviceToHost));
+        if (run2 > 0)
+            CK(cudaMemcpy2D(vec_bits_host + (size_t)run1 * h->dim, (size_t)h->dim * 2, h->vec, (size_t)h->ld * 2,
+                            (size_t)h->dim * 2, (size_t)run2, cudaMemcpyDeviceToHost));
+    }
+#define EXPORT_COL(dst, src, T)                                                                       \
+    if (dst) {                                                                                        \
+        CK(cudaMemcpy(dst, (const T*)src + h->head, (size_t)run1 * sizeof(T), cudaMemcpyDeviceToHost)); \
+        if (run2 > 0) CK(cudaMemcpy(dst + run1, src, (size_t)run2 * sizeof(T), cudaMemcpyDeviceToHost)); \
+    }
+    EXPORT_COL(inv_norm_host, h->inv_norm, float)
+    EXPORT_COL(prio_host, h->prio, int32_t)
+    EXPORT_COL(tagmask_host, h->tagmask, uint64_t)
+    EXPORT_COL(expires_us_host, h->expires, int64_t)
+#undef EXPORT_COL
+    return PILOTT_OK;
+}
+
+int pilott_topk_merge(const int64_t* idx_dev, const double* score64_dev, int n_shards, int64_t nq, int k,
+                      int64_t* out_idx_dev, float* out_score_dev, double* out_score64_dev, void* stream) {
+    if (nq < 0 || n_shards < 1 || k < 1) return fail(PILOTT_EINVAL, "bad merge shape");
+    if ((int64_t)n_shards * k > 2048) return fail(PILOTT_EINVAL, "n_shards * k must be <= 2048");
+    if (nq > 0 && (!idx_dev || !score64_dev || !out_idx_dev || !out_score_dev)) return fail(PILOTT_EINVAL, "NULL pointer");
+    CK(pilott::launch_topk_merge(idx_dev, score64_dev, n_shards, nq, k, out_idx_dev, out_score_dev,
+                                 out_score64_dev, (cudaStream_t)stream));
+    return PILOTT_OK;
+}
+
+int pilott_route_score(const uint64_t* task_req_dev, const uint64_t* task_tags_dev, const int32_t* task_type_dev,
+                       const uint8_t* task_flags_dev, int64_t nt, const uint64_t* agent_caps_dev,
+                       const uint64_t* agent_spec_dev, const uint8_t* agent_flags_dev,
+                       const double* agent_s12_dev, const double* agent_t4_dev, int na, int words,
+                       const double* spec_u_dev, int max_tags, int mode, int32_t* out_agent_dev,
+                       double* out_score_dev, void* stream) {
+    if (nt < 0 || na < 0) return fail(PILOTT_EINVAL, "negative size");
+    if (words < 1 || words > 64) return fail(PILOTT_EINVAL, "words must be in [1, 64]");
+    if (max_tags < 64 * words) return fail(PILOTT_EINVAL, "max_tags must be >= 64*words");
+    if (mode < 0 || mode > 2) return fail(PILOTT_EINVAL, "mode must be 0, 1 or 2");
+    if (nt == 0) return PILOTT_OK;
+    if (!task_req_dev || !task_tags_dev || !task_type_dev || !task_flags_dev || !out_agent_dev || !out_score_dev)
+        return fail(PILOTT_EINVAL, "NULL task or output pointer");
+    if (na > 0 && (!agent_caps_dev || !agent_spec_dev || !agent_flags_dev || !agent_s12_dev || !agent_t4_dev || !spec_u_dev))
+        return fail(PILOTT_EINVAL, "NULL agent table pointer");
+    CK(pilott::launch_route(task_req_dev, task_tags_dev, task_type_dev, task_flags_dev, nt, agent_caps_dev,
+                            agent_spec_dev, agent_flags_dev, agent_s12_dev, agent_t4_dev, na, words, spec_u_dev,
+                            max_tags, mode, out_agent_dev, out_score_dev, (cudaStream_t)stream));
+    return PILOTT_OK;
+}
+
+int pilott_task_priority(const uint8_t* urgent_dev, const int32_t* complexity_dev, const int32_t* n_deps_dev,
+                         int64_t nt, uint8_t* out_dev, void* stream) {
+    if (nt < 0) return fail(PILOTT_EINVAL, "negative size");
+    if (nt == 0) return PILOTT_OK;
+    if (!urgent_dev || !complexity_dev || !n_deps_dev || !out_dev) return fail(PILOTT_EINVAL, "NULL pointer");
+    CK(pilott::launch_task_priority(urgent_dev, complexity_dev, n_deps_dev, nt, out_dev, (cudaStream_t)stream));
+    return PILOTT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,104 @@
+// common.cuh -- shared device helpers for the pilott_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace pilott {
+
+constexpr int KP = 32;    // candidates kept per (query, slot) by the approximate pass
+constexpr int CAP = 64;   // per-row append buffer (KP survivors + pending appends)
+constexpr unsigned FULL = 0xffffffffu;
+
+// ---- order-preserving float <-> uint32, and the 64-bit candidate key -------------------
+// key = ord(score) << 32 | (0xFFFFFFFF - age):  larger key == better candidate
+// (higher score first, then OLDER row first: the reference returns older items first
+//  among equals, pilott/memory/enhanced_memory.py:114).  key 0 == empty.
+__device__ __forceinline__ uint32_t f2ord(float f) {
+    uint32_t u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float ord2f(uint32_t o) {
+    return __uint_as_float((o & 0x80000000u) ? (o & 0x7fffffffu) : ~o);
+}
+__device__ __forceinline__ uint64_t make_key(float s, uint32_t age) {
+    return ((uint64_t)f2ord(s) << 32) | (uint64_t)(0xFFFFFFFFu - age);
+}
+__device__ __forceinline__ uint32_t key_age(uint64_t k) { return 0xFFFFFFFFu - (uint32_t)k; }
+__device__ __forceinline__ float key_score(uint64_t k) { return ord2f((uint32_t)(k >> 32)); }
+
+__device__ __forceinline__ uint64_t shfl_xor64(uint64_t v, int m) {
+    uint32_t lo = __shfl_xor_sync(FULL, (uint32_t)v, m);
+    uint32_t hi = __shfl_xor_sync(FULL, (uint32_t)(v >> 32), m);
+    return ((uint64_t)hi << 32) | lo;
+}
+__device__ __forceinline__ uint64_t shfl64(uint64_t v, int src) {
+    uint32_t lo = __shfl_sync(FULL, (uint32_t)v, src);
+    uint32_t hi = __shfl_sync(FULL, (uint32_t)(v >> 32), src);
+    return ((uint64_t)hi << 32) | lo;
+}
+
+// Bitonic sort of one 64-bit key per lane across the warp.  DESC: lane 0 ends largest.
+template <bool DESC>
+__device__ __forceinline__ uint64_t warp_sort64(uint64_t v, int lane) {
+#pragma unroll
+    for (int k = 2; k <= 32; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            const uint64_t o = shfl_xor64(v, j);
+            const bool up = (((lane & k) == 0) != DESC);
+            const bool lower = (lane & j) == 0;
+            const bool keep_min = (lower == up);
+            const uint64_t mn = v < o ? v : o, mx = v < o ? o : v;
+            v = keep_min ? mn : mx;
+        }
+    }
+    return v;
+}
+__device__ __forceinline__ uint64_t warp_min64(uint64_t v) {
+#pragma unroll
+    for (int j = 16; j > 0; j >>= 1) {
+        const uint64_t o = shfl_xor64(v, j);
+        v = v < o ? v : o;
+    }
+    return v;
+}
+
+// Keep the KP best of a row buffer holding cnt (<= CAP) keys.  Whole warp cooperates.
+// Leaves the survivors (unsorted, empty = 0) in buf[0..KP) and returns them per lane.
+__device__ __forceinline__ uint64_t warp_prune(uint64_t* buf, int cnt, int lane, int& new_cnt,
+                                               float& new_thr) {
+    uint64_t a = lane < cnt ? buf[lane] : 0ull;
+    uint64_t b = (lane + 32) < cnt ? buf[lane + 32] : 0ull;
+    a = warp_sort64<true>(a, lane);
+    b = warp_sort64<false>(b, lane);
+    const uint64_t m = a > b ? a : b;          // half-cleaner of a bitonic sequence: the top 32
+    const uint64_t mn = warp_min64(m);
+    buf[lane] = m;
+    new_cnt = cnt < KP ? cnt : KP;
+    new_thr = cnt >= KP ? key_score(mn) : -INFINITY;
+    return m;
+}
+
+// Prune every row of this warp's 32-row group whose bit is set in `mask`.
+// rows = base of the warp's 32 row buffers (row r at rows + r*CAP).
+__device__ __forceinline__ void warp_prune_rows(unsigned mask, uint64_t* rows, int lane, int& cnt,
+                                                float& thr) {
+    __syncwarp();
+    while (mask) {
+        const int r = __ffs(mask) - 1;
+        mask &= mask - 1;
+        const int c = __shfl_sync(FULL, cnt, r);
+        int nc;
+        float nt;
+        warp_prune(rows + r * CAP, c, lane, nc, nt);
+        if (lane == r) { cnt = nc; thr = nt; }
+    }
+    __syncwarp();
+}
+
+__device__ __forceinline__ float bf16_bits_to_float(uint16_t b) {
+    return __uint_as_float(((uint32_t)b) << 16);
+}
+
+}  // namespace pilott

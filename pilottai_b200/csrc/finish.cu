@@ -1,0 +1,272 @@
+// finish.cu -- K4: merge the per-slot candidate lists, re-score the survivors exactly in
+// fp64 in the oracle's order, sort by (score desc, insertion sequence asc), gap-check.
+// Also: the brute-force exact search (fallback / large k) and the multi-GPU top-k merge.
+#include "common.cuh"
+#include "internal.h"
+
+namespace pilott {
+
+// (score desc, seq asc): true when a ranks strictly before b.
+__device__ __forceinline__ bool ranks_before(double sa, int64_t qa, double sb, int64_t qb) {
+    return sa > sb || (sa == sb && qa < qb);
+}
+
+__device__ __forceinline__ double shfl_xor_d(double v, int m) {
+    return __longlong_as_double((long long)shfl_xor64((uint64_t)__double_as_longlong(v), m));
+}
+
+// Bitonic sort of (score, seq) pairs, one per lane; lane 0 ends with the best.
+__device__ __forceinline__ void warp_sort_pairs(double& s, int64_t& q, int lane) {
+#pragma unroll
+    for (int k = 2; k <= 32; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            const double os = shfl_xor_d(s, j);
+            const int64_t oq = (int64_t)shfl_xor64((uint64_t)q, j);
+            const bool desc_block = ((lane & k) == 0);        // best-first in this block
+            const bool lower = (lane & j) == 0;
+            const bool want_best = (lower == desc_block);
+            const bool other_better = ranks_before(os, oq, s, q);
+            if (want_best == other_better) { s = os; q = oq; }
+        }
+    }
+}
+
+// Exact cosine of one query / one row, fp64, d = 0..ld-1 in order (padding columns are
+// zeros and add exactly nothing).  Every lane computes its own row; the query is read
+// through the read-only path (same address in all lanes -> broadcast).
+__device__ __forceinline__ double exact_cosine(const __nv_bfloat16* __restrict__ qrow,
+                                               const __nv_bfloat16* __restrict__ mrow, int ld,
+                                               double* nq_out = nullptr) {
+    double dot = 0.0, nq = 0.0, nm = 0.0;
+    for (int c = 0; c < ld; c += 8) {
+        const uint4 qv = __ldg(reinterpret_cast<const uint4*>(qrow + c));
+        const uint4 mv = __ldg(reinterpret_cast<const uint4*>(mrow + c));
+        const uint32_t qw[4] = {qv.x, qv.y, qv.z, qv.w}, mw[4] = {mv.x, mv.y, mv.z, mv.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const double q0 = (double)__uint_as_float(qw[j] << 16);
+            const double q1 = (double)__uint_as_float(qw[j] & 0xffff0000u);
+            const double m0 = (double)__uint_as_float(mw[j] << 16);
+            const double m1 = (double)__uint_as_float(mw[j] & 0xffff0000u);
+            dot = __fma_rn(q0, m0, dot); nq = __fma_rn(q0, q0, nq); nm = __fma_rn(m0, m0, nm);
+            dot = __fma_rn(q1, m1, dot); nq = __fma_rn(q1, q1, nq); nm = __fma_rn(m1, m1, nm);
+        }
+    }
+    if (nq_out) *nq_out = nq;
+    const double den = __dmul_rn(__dsqrt_rn(nq), __dsqrt_rn(nm));
+    return den > 0.0 ? __ddiv_rn(dot, den) : 0.0;
+}
+
+// One warp per query.
+__global__ void __launch_bounds__(128)
+finish_kernel(const uint64_t* __restrict__ partials, int slots, const __nv_bfloat16* __restrict__ qb,
+              const __nv_bfloat16* __restrict__ vec, int ld, int64_t nq, int64_t capacity,
+              int64_t head, int64_t base_seq, int k, double err, int64_t* __restrict__ out_idx,
+              float* __restrict__ out_score, double* __restrict__ out_score64,
+              uint8_t* __restrict__ flags, int32_t* __restrict__ inexact) {
+    const int lane = threadIdx.x & 31;
+    const int64_t q = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (q >= nq) return;
+    // 1. top-KP of all slots' candidates by approximate key
+    const uint64_t* p = partials + q * slots * KP;
+    uint64_t best = warp_sort64<true>(p[lane], lane);
+    for (int s = 1; s < slots; ++s) {
+        const uint64_t x = warp_sort64<false>(p[s * KP + lane], lane);
+        best = warp_sort64<true>(best > x ? best : x, lane);
+    }
+    const uint64_t worst = shfl64(best, 31);
+    const bool pool_full = worst != 0ull;                  // something may have been dropped
+    // 2. exact re-score
+    const bool valid = best != 0ull;
+    double sc = -INFINITY;
+    int64_t seq = INT64_MAX;
+    const __nv_bfloat16* qrow = qb + q * ld;
+    double nqn = 0.0;                                      // lane 0 is valid whenever pool_full
+    if (valid) {
+        const uint32_t age = key_age(best);
+        int64_t slot = head + age;
+        if (slot >= capacity) slot -= capacity;
+        sc = exact_cosine(qrow, vec + slot * ld, ld, &nqn);
+        seq = base_seq + age;
+    }
+    // 3. final order
+    warp_sort_pairs(sc, seq, lane);
+    if (lane < k) {
+        const bool ok = seq != INT64_MAX;
+        out_idx[q * k + lane] = ok ? seq : -1;
+        out_score[q * k + lane] = ok ? (float)sc : -INFINITY;
+        if (out_score64) out_score64[q * k + lane] = ok ? sc : -INFINITY;
+    }
+    // 4. gap check: every row dropped by the approximate pass has approximate score <=
+    // the worst kept one; it cannot reach the exact k-th score if the gap exceeds err.
+    const double e_k = __longlong_as_double((long long)shfl64((uint64_t)__double_as_longlong(sc), k - 1));
+    if (lane == 0) {
+        bool bad = false;
+        if (pool_full) {
+            const double a_min = nqn > 0.0 ? (double)key_score(worst) / sqrt(nqn) : 0.0;
+            bad = !(a_min + err < e_k);
+        }
+        if (flags) flags[q] = bad ? 1 : 0;
+        if (bad && inexact) atomicAdd(inexact, 1);
+    }
+}
+
+cudaError_t launch_finish(const FinishArgs& a, cudaStream_t st) {
+    if (a.nq <= 0) return cudaSuccess;
+    const int wpb = 4;
+    finish_kernel<<<(unsigned)((a.nq + wpb - 1) / wpb), wpb * 32, 0, st>>>(
+        a.partials, a.slots, (const __nv_bfloat16*)a.qb, (const __nv_bfloat16*)a.vec, a.ld, a.nq,
+        a.capacity, a.head, a.base_seq, a.k, a.err, a.out_idx, a.out_score, a.out_score64,
+        a.flags, a.inexact);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------
+// Brute-force exact search.  Pass 1: fp64 score of every candidate row (NaN = filtered).
+// Pass 2: k rounds of "best key strictly after the previous one", one CTA per query.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+exact_scores_kernel(const __nv_bfloat16* __restrict__ qb, const __nv_bfloat16* __restrict__ vec, int ld,
+                    const int32_t* __restrict__ prio, const uint64_t* __restrict__ tagmask,
+                    const int64_t* __restrict__ expires, int64_t nslots, const int32_t* __restrict__ qids,
+                    int32_t min_prio, uint64_t req, int64_t now_us, double* __restrict__ scratch) {
+    const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= nslots) return;
+    const int sel = blockIdx.y;
+    const int64_t q = qids ? qids[sel] : sel;
+    const int64_t e = expires[n];
+    const bool ok = prio[n] >= min_prio && (tagmask[n] & req) == req && !(e != 0 && now_us > e);
+    double s = __longlong_as_double(0x7ff8000000000000ll);
+    if (ok) s = exact_cosine(qb + q * ld, vec + n * ld, ld);
+    scratch[(int64_t)sel * nslots + n] = s;
+}
+
+__global__ void __launch_bounds__(1024)
+exact_select_kernel(const double* __restrict__ scratch, int64_t nslots, int64_t capacity, int64_t head,
+                    int64_t base_seq, const int32_t* __restrict__ qids, int k,
+                    int64_t* __restrict__ out_idx, float* __restrict__ out_score,
+                    double* __restrict__ out_score64) {
+    __shared__ double s_sc[32];
+    __shared__ int64_t s_age[32];
+    __shared__ double prev_sc;
+    __shared__ int64_t prev_age;
+    const int sel = blockIdx.x;
+    const int64_t q = qids ? qids[sel] : sel;
+    const double* sc = scratch + (int64_t)sel * nslots;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) { prev_sc = INFINITY; prev_age = -1; }
+    __syncthreads();
+    for (int r = 0; r < k; ++r) {
+        const double ps = prev_sc;
+        const int64_t pa = prev_age;
+        double bs = -INFINITY;
+        int64_t ba = INT64_MAX;               // INT64_MAX == nothing found
+        for (int64_t n = threadIdx.x; n < nslots; n += blockDim.x) {
+            const double s = sc[n];
+            if (s != s) continue;             // filtered
+            int64_t age = n - head;
+            if (age < 0) age += capacity;
+            const bool after_prev = ranks_before(ps, pa, s, age);
+            if (after_prev && (ba == INT64_MAX || ranks_before(s, age, bs, ba))) { bs = s; ba = age; }
+        }
+#pragma unroll
+        for (int j = 16; j > 0; j >>= 1) {
+            const double os = shfl_xor_d(bs, j);
+            const int64_t oa = (int64_t)shfl_xor64((uint64_t)ba, j);
+            if (oa != INT64_MAX && (ba == INT64_MAX || ranks_before(os, oa, bs, ba))) { bs = os; ba = oa; }
+        }
+        if (lane == 0) { s_sc[warp] = bs; s_age[warp] = ba; }
+        __syncthreads();
+        if (warp == 0) {
+            bs = s_sc[lane]; ba = s_age[lane];
+#pragma unroll
+            for (int j = 16; j > 0; j >>= 1) {
+                const double os = shfl_xor_d(bs, j);
+                const int64_t oa = (int64_t)shfl_xor64((uint64_t)ba, j);
+                if (oa != INT64_MAX && (ba == INT64_MAX || ranks_before(os, oa, bs, ba))) { bs = os; ba = oa; }
+            }
+            if (lane == 0) {
+                const bool ok = ba != INT64_MAX;
+                out_idx[q * k + r] = ok ? base_seq + ba : -1;
+                out_score[q * k + r] = ok ? (float)bs : -INFINITY;
+                if (out_score64) out_score64[q * k + r] = ok ? bs : -INFINITY;
+                // once nothing is found, nothing will be found again: park the cursor at the end
+                prev_sc = ok ? bs : -INFINITY;
+                prev_age = ok ? ba : INT64_MAX;
+            }
+        }
+        __syncthreads();
+    }
+}
+
+cudaError_t launch_exact(const void* qb, const void* vec, int ld, const int32_t* prio,
+                         const uint64_t* tagmask, const int64_t* expires, int64_t nslots,
+                         int64_t capacity, int64_t head, int64_t base_seq, const int32_t* qids,
+                         int64_t nsel, int k, int32_t min_prio, uint64_t req, int64_t now_us,
+                         double* scratch, int64_t* out_idx, float* out_score, double* out_score64,
+                         cudaStream_t st) {
+    if (nsel <= 0) return cudaSuccess;
+    if (nslots > 0) {
+        dim3 grid((unsigned)((nslots + 127) / 128), (unsigned)nsel);
+        exact_scores_kernel<<<grid, 128, 0, st>>>((const __nv_bfloat16*)qb, (const __nv_bfloat16*)vec,
+                                                  ld, prio, tagmask, expires, nslots, qids,
+                                                  min_prio, req, now_us, scratch);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    exact_select_kernel<<<(unsigned)nsel, 1024, 0, st>>>(scratch, nslots, capacity, head, base_seq,
+                                                         qids, k, out_idx, out_score, out_score64);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------
+// Multi-GPU merge: [shards, nq, k] exact (score, idx) lists -> global top-k per query by
+// rank counting (shards*k <= 256 candidates; pairs are unique because idx is).
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+topk_merge_kernel(const int64_t* __restrict__ idx, const double* __restrict__ sc, int shards, int64_t nq,
+                  int k, int64_t* __restrict__ out_idx, float* __restrict__ out_score,
+                  double* __restrict__ out_score64) {
+    extern __shared__ __align__(16) unsigned char sm_raw[];
+    const int total = shards * k;
+    double* s_sc = reinterpret_cast<double*>(sm_raw);
+    int64_t* s_idx = reinterpret_cast<int64_t*>(s_sc + total);
+    const int64_t q = blockIdx.x;
+    for (int i = threadIdx.x; i < total; i += blockDim.x) {
+        const int sh = i / k, j = i % k;
+        s_sc[i] = sc[((int64_t)sh * nq + q) * k + j];
+        s_idx[i] = idx[((int64_t)sh * nq + q) * k + j];
+    }
+    for (int j = threadIdx.x; j < k; j += blockDim.x) {
+        out_idx[q * k + j] = -1;
+        out_score[q * k + j] = -INFINITY;
+        if (out_score64) out_score64[q * k + j] = -INFINITY;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < total; i += blockDim.x) {
+        const int64_t me = s_idx[i];
+        if (me < 0) continue;
+        const double ms = s_sc[i];
+        int rank = 0;
+        for (int j = 0; j < total; ++j)
+            if (s_idx[j] >= 0 && ranks_before(s_sc[j], s_idx[j], ms, me)) ++rank;
+        if (rank < k) {
+            out_idx[q * k + rank] = me;
+            out_score[q * k + rank] = (float)ms;
+            if (out_score64) out_score64[q * k + rank] = ms;
+        }
+    }
+}
+
+cudaError_t launch_topk_merge(const int64_t* idx, const double* sc, int shards, int64_t nq, int k,
+                              int64_t* out_idx, float* out_score, double* out_score64,
+                              cudaStream_t st) {
+    if (nq <= 0) return cudaSuccess;
+    const size_t smem = (size_t)shards * k * 16;
+    topk_merge_kernel<<<(unsigned)nq, 256, smem, st>>>(idx, sc, shards, nq, k, out_idx, out_score,
+                                                       out_score64);
+    return cudaGetLastError();
+}
+
+}  // namespace pilott

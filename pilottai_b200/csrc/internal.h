@@ -1,0 +1,80 @@
+// internal.h -- host-side launch wrappers shared between the translation units.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace pilott {
+
+struct ScanArgs {
+    const void* qb;          // bf16 [nq_pad, ld] converted queries
+    const void* vec;         // bf16 [capacity, ld]
+    const float* scale;      // [cap_pad]: inverse norm, NaN for masked / unused slots
+    uint64_t* partials;      // [nq][slots][KP] candidate keys
+    int64_t nq;
+    int64_t nslots;          // physical slots holding rows (= min(total, capacity))
+    int64_t capacity;
+    int64_t head;            // physical slot of the oldest row
+    int ld;                  // row stride in elements (multiple of 64)
+    int slots;               // partial lists per query
+};
+
+// generic CUDA-core scan (any shape).  Returns slots used via args.slots (caller sets).
+cudaError_t launch_scan_generic(const ScanArgs& a, int num_sms, cudaStream_t st);
+int scan_generic_slots(int64_t nq, int64_t nslots, int num_sms);
+
+// tcgen05 scan.  cg = 1 or 2.
+cudaError_t launch_scan_tc(const ScanArgs& a, const CUtensorMap* map_q, const CUtensorMap* map_c,
+                           int cg, int ctas, cudaStream_t st);
+int scan_tc_slots(int64_t nq, int64_t nslots, int cg, int ctas);
+cudaError_t scan_tc_init();   // opt-in shared memory attributes
+
+cudaError_t launch_append(const float* x, int64_t n, int dim, int ld, void* vec, float* inv_norm,
+                          int32_t* prio, uint64_t* tagmask, int64_t* expires,
+                          const int32_t* in_prio, const uint64_t* in_tag, const int64_t* in_exp,
+                          int64_t first_slot, int64_t capacity, cudaStream_t st);
+cudaError_t launch_convert_queries(const float* q, int64_t nq, int dim, int ld, void* qb,
+                                   cudaStream_t st);
+cudaError_t launch_scale(const float* inv_norm, const int32_t* prio, const uint64_t* tagmask,
+                         const int64_t* expires, int64_t nslots, int64_t cap_pad, int32_t min_prio,
+                         uint64_t req, int64_t now_us, float* scale, cudaStream_t st);
+
+struct FinishArgs {
+    const uint64_t* partials; int slots;
+    const void* qb; const void* vec; int ld;
+    int64_t nq, capacity, head, base_seq;
+    int k; double err;
+    int64_t* out_idx; float* out_score; double* out_score64;
+    uint8_t* flags; int32_t* inexact;
+};
+cudaError_t launch_finish(const FinishArgs& a, cudaStream_t st);
+
+cudaError_t launch_exact(const void* qb, const void* vec, int ld, const int32_t* prio,
+                         const uint64_t* tagmask, const int64_t* expires, int64_t nslots,
+                         int64_t capacity, int64_t head, int64_t base_seq, const int32_t* qids,
+                         int64_t nsel, int k, int32_t min_prio, uint64_t req, int64_t now_us,
+                         double* scratch, int64_t* out_idx, float* out_score, double* out_score64,
+                         cudaStream_t st);
+
+cudaError_t launch_topk_merge(const int64_t* idx, const double* sc, int shards, int64_t nq, int k,
+                              int64_t* out_idx, float* out_score, double* out_score64,
+                              cudaStream_t st);
+
+cudaError_t launch_compact_flags(const int64_t* expires, int64_t count, int64_t head,
+                                 int64_t capacity, int64_t now_us, uint8_t* keep, cudaStream_t st);
+cudaError_t launch_gather_rows(const void* vec, const float* inv_norm, const int32_t* prio,
+                               const uint64_t* tagmask, const int64_t* expires, int ld,
+                               const int64_t* src_slot, int64_t n, void* dvec, float* dinv,
+                               int32_t* dprio, uint64_t* dtag, int64_t* dexp, cudaStream_t st);
+
+cudaError_t launch_route(const uint64_t* task_req, const uint64_t* task_tags,
+                         const int32_t* task_type, const uint8_t* task_flags, int64_t nt,
+                         const uint64_t* agent_caps,
+                         const uint64_t* agent_spec, const uint8_t* agent_flags,
+                         const double* agent_s12, const double* agent_t4, int na, int words,
+                         const double* spec_u, int max_tags, int mode, int32_t* out_agent,
+                         double* out_score, cudaStream_t st);
+cudaError_t launch_task_priority(const uint8_t* urgent, const int32_t* complexity,
+                                 const int32_t* ndeps, int64_t nt, uint8_t* out, cudaStream_t st);
+
+}  // namespace pilott

@@ -1,0 +1,400 @@
+// scan_tc.cu -- K2+K3: query x memory similarity on tcgen05 tensor cores with the
+// norm/mask/score epilogue and the streaming top-KP select fused in.  sm_100a only.
+//
+// GEMM view: D[query, row] = sum_d Q[query, d] * M[row, d]   (both operands K-major bf16,
+// fp32 accumulation in TMEM).  The Q x N score matrix never reaches HBM: each epilogue
+// thread owns one query row of the accumulator tile (TMEM lane == query), multiplies by
+// the row's scale (inverse norm, NaN when filtered) and compares against its running
+// threshold; the rare survivors are appended to a shared-memory candidate buffer that a
+// whole warp prunes back to KP entries when it fills (common.cuh).
+//
+// Work split: a CTA (CG=1) or CTA pair (CG=2) is bound to ONE query tile for its whole
+// life and sweeps a contiguous range of 256-row corpus tiles ("slot"), so the selection
+// state stays on chip; the per-slot candidate lists are merged by finish.cu.
+//
+// Warp roles (256 threads): 0 = TMA producer, 1 = MMA issuer, 2 = TMEM allocator,
+// 3 = idle, 4..7 = epilogue (TMEM lane quarter = warp % 4).
+// Pipelines: smem full/empty ring (TMA <-> MMA), TMEM full/empty x2 (MMA <-> epilogue).
+#include "common.cuh"
+#include "internal.h"
+
+namespace pilott {
+
+constexpr int BM = 128;        // query rows per CTA (TMEM lanes)
+constexpr int BN = 256;        // corpus rows per tile (UMMA N, TMEM columns per stage)
+constexpr int BK = 64;         // bf16 elements per k-block = one 128-byte swizzle atom
+constexpr int UK = 16;         // UMMA K for 16-bit inputs
+constexpr int ACC_STAGES = 2;  // 2 x 256 TMEM columns
+
+template <int CG> struct TcCfg {
+    static constexpr int STAGES = CG == 1 ? 3 : 4;
+    static constexpr int A_BYTES = BM * BK * 2;                    // 16 KB
+    static constexpr int B_ROWS = BN / CG;                         // rows of B this CTA loads
+    static constexpr int B_BYTES = B_ROWS * BK * 2;                // 32 KB / 16 KB
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int BUF_BYTES = BM * CAP * 8;                 // 64 KB candidate buffers
+    static constexpr int BAR_BYTES = 256;
+    static constexpr int SMEM = 1024 /*align slack*/ + STAGES * STAGE_BYTES + BUF_BYTES + BAR_BYTES;
+};
+
+// ---- PTX wrappers ----------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+// arrive on the same barrier in CTA `rank` of the cluster
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t rank) {
+    asm volatile(
+        "{\n\t.reg .b32 ra;\n\t"
+        "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+        "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}"
+        ::"r"(bar), "r"(rank) : "memory");
+}
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
+// Bounded wait: a protocol bug traps (launch failure) instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    if (mbar_try_wait(bar, parity)) return;
+    const long long t0 = clock64();
+    while (!mbar_try_wait(bar, parity)) {
+        if (clock64() - t0 > 4000000000ll) __trap();
+    }
+}
+
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+// CTA-pair variant: the mbarrier may live in the peer (leader) CTA's shared memory.
+__device__ __forceinline__ void tma_load_2d_cg2(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar_cluster) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar_cluster), "r"(c0), "r"(c1) : "memory");
+}
+
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+template <int CG> __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
+    if (CG == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    } else {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+}
+template <int CG> __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+    if (CG == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+    else asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+
+// D[tmem] (+)= A[smem desc] * B[smem desc]
+template <int CG> __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    if (CG == 1) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+            ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+    } else {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+            ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+    }
+}
+// Arrive on `bar` once every tcgen05.mma issued so far has completed (CG=2: in both CTAs).
+template <int CG> __device__ __forceinline__ void umma_commit(uint32_t bar) {
+    if (CG == 1) {
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+    } else {
+        const uint16_t mask = 3;
+        asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                     ::"r"(bar), "h"(mask) : "memory");
+    }
+}
+
+// K-major, 128-byte swizzle shared-memory matrix descriptor (sm_100 format):
+// [0,14) start>>4, [16,30) leading byte offset>>4 (unused for swizzled K-major),
+// [32,46) stride byte offset>>4 = 1024 B between 8-row groups, [46,48) version = 1,
+// [61,64) layout = 2 (SWIZZLE_128B).
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+    d |= (uint64_t)(1024 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+// kind::f16 instruction descriptor: D=f32 (bit4), A=B=bf16 (bits 7,10), K-major both,
+// N>>3 at [17,23), M>>4 at [24,29).
+__host__ __device__ constexpr uint32_t make_idesc(int m, int n) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+__device__ __forceinline__ float4 ldg_nc_f4(const float* p) {
+    float4 r;
+    asm volatile("ld.global.nc.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+// ---- the kernel ------------------------------------------------------------------------
+// Grid: `units` work units (CTAs for CG=1, CTA pairs for CG=2).  Unit u serves query group
+// u % groups (BM*CG query rows) and slot u / groups of that group.
+template <int CG>
+__global__ void __launch_bounds__(256, 1)
+scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_c,
+               const float* __restrict__ scale, uint64_t* __restrict__ partials, int64_t nq,
+               int64_t nslots, int64_t capacity, int64_t head, int kblocks, int slots, int groups) {
+    using Cfg = TcCfg<CG>;
+    extern __shared__ unsigned char smem_dyn[];
+    const uint32_t base = (smem_u32(smem_dyn) + 1023u) & ~1023u;        // 1024-B aligned (swizzle atom)
+    unsigned char* base_ptr = smem_dyn + (base - smem_u32(smem_dyn));
+    const uint32_t stage_base = base;
+    uint64_t* bufs = reinterpret_cast<uint64_t*>(base_ptr + Cfg::STAGES * Cfg::STAGE_BYTES);
+    const uint32_t bar_base = base + Cfg::STAGES * Cfg::STAGE_BYTES + Cfg::BUF_BYTES;
+    // barrier layout (8 B each): full[STAGES], empty[STAGES], tfull[2], tempty[2], then tmem ptr
+    const uint32_t bar_full = bar_base;
+    const uint32_t bar_empty = bar_base + 8 * Cfg::STAGES;
+    const uint32_t bar_tfull = bar_base + 16 * Cfg::STAGES;
+    const uint32_t bar_tempty = bar_tfull + 8 * ACC_STAGES;
+    const uint32_t tmem_slot = bar_tempty + 8 * ACC_STAGES;
+    volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(
+        base_ptr + Cfg::STAGES * Cfg::STAGE_BYTES + Cfg::BUF_BYTES + 16 * Cfg::STAGES + 16 * ACC_STAGES);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = CG == 2 ? cluster_ctarank() : 0u;
+    const bool leader = rank == 0;
+    const int unit = CG == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+    const int group = unit % groups, slot = unit / groups;
+    const int64_t q0 = ((int64_t)group * CG + rank) * BM;               // this CTA's first query row
+    const int64_t ntiles = (nslots + BN - 1) / BN;
+    const int64_t t_lo = ntiles * slot / slots, t_hi = ntiles * (slot + 1) / slots;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_q) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_c) : "memory");
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < Cfg::STAGES; ++i) {
+            mbar_init(bar_full + 8 * i, 1);
+            mbar_init(bar_empty + 8 * i, 1);
+        }
+        for (int i = 0; i < ACC_STAGES; ++i) {
+            mbar_init(bar_tfull + 8 * i, 1);
+            mbar_init(bar_tempty + 8 * i, 4 * CG);     // one arrive per epilogue warp per CTA
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) tmem_alloc<CG>(tmem_slot, 512);
+    tc_fence_before();
+    if (CG == 2) cluster_sync_all(); else __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot_ptr;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (lane == 0) {
+            const uint32_t full0 = CG == 2 ? mapa_u32(bar_full, 0) : bar_full;   // leader's barriers
+            int stage = 0; uint32_t phase = 0;
+            for (int64_t t = t_lo; t < t_hi; ++t) {
+                const int n0 = (int)(t * BN) + (int)rank * Cfg::B_ROWS;
+                for (int kb = 0; kb < kblocks; ++kb) {
+                    mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+                    const uint32_t sa = stage_base + stage * Cfg::STAGE_BYTES;
+                    const uint32_t sb = sa + Cfg::A_BYTES;
+                    if (CG == 1) {
+                        mbar_arrive_expect_tx(bar_full + 8 * stage, Cfg::STAGE_BYTES);
+                        tma_load_2d(sa, &map_q, kb * BK, (int)q0, bar_full + 8 * stage);
+                        tma_load_2d(sb, &map_c, kb * BK, n0, bar_full + 8 * stage);
+                    } else {
+                        if (leader) mbar_arrive_expect_tx(bar_full + 8 * stage, 2 * Cfg::STAGE_BYTES);
+                        tma_load_2d_cg2(sa, &map_q, kb * BK, (int)q0, full0 + 8 * stage);
+                        tma_load_2d_cg2(sb, &map_c, kb * BK, n0, full0 + 8 * stage);
+                    }
+                    if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ===== MMA issuer (leader CTA only in pair mode) =====
+        if (lane == 0 && leader) {
+            constexpr uint32_t idesc = make_idesc(BM * CG, BN);
+            int stage = 0; uint32_t phase = 0;
+            int as = 0; uint32_t aphase = 0;
+            for (int64_t t = t_lo; t < t_hi; ++t) {
+                mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * BN;
+                for (int kb = 0; kb < kblocks; ++kb) {
+                    mbar_wait(bar_full + 8 * stage, phase);
+                    tc_fence_after();
+                    const uint32_t sa = stage_base + stage * Cfg::STAGE_BYTES;
+                    const uint64_t adesc = make_desc(sa), bdesc = make_desc(sa + Cfg::A_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BK / UK; ++k) {
+                        // +32 bytes per UMMA_K step inside the 128-byte swizzle atom
+                        umma_bf16<CG>(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                    }
+                    umma_commit<CG>(bar_empty + 8 * stage);       // frees the smem stage when the MMAs retire
+                    if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+                }
+                umma_commit<CG>(bar_tfull + 8 * as);              // accumulator tile complete
+                if (++as == ACC_STAGES) { as = 0; aphase ^= 1; }
+            }
+        }
+        __syncwarp();
+    } else if (warp >= 4) {
+        // ===== epilogue: scale, threshold, append, prune =====
+        const int quarter = warp & 3;                              // TMEM lanes [32*quarter, +32)
+        const int row = quarter * 32 + lane;                       // query row within the CTA tile
+        uint64_t* rows = bufs + (size_t)quarter * 32 * CAP;
+        uint64_t* mine = bufs + (size_t)row * CAP;
+        float thr = -INFINITY;
+        int cnt = 0;
+        int as = 0; uint32_t aphase = 0;
+        for (int64_t t = t_lo; t < t_hi; ++t) {
+            const int64_t n0 = t * BN;
+            mbar_wait(bar_tfull + 8 * as, aphase);
+            tc_fence_after();
+            const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                uint32_t v[32];
+                tmem_ld32(taddr0 + c, v);
+                const float* sp = scale + n0 + c;
+#pragma unroll
+                for (int g8 = 0; g8 < 4; ++g8) {
+                    const float4 s0 = ldg_nc_f4(sp + g8 * 8);
+                    const float4 s1 = ldg_nc_f4(sp + g8 * 8 + 4);
+                    const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float s = __uint_as_float(v[g8 * 8 + j]) * sc[j];
+                        if (s >= thr) {
+                            int64_t age = n0 + c + g8 * 8 + j - head;
+                            if (age < 0) age += capacity;
+                            mine[cnt++] = make_key(s, (uint32_t)age);
+                        }
+                    }
+                    const unsigned full = __ballot_sync(FULL, cnt > CAP - 8);
+                    if (full) warp_prune_rows(full, rows, lane, cnt, thr);
+                }
+            }
+            // release this accumulator stage to the MMA issuer (in the leader CTA)
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                if (CG == 2) mbar_arrive_cluster(bar_tempty + 8 * as, 0);
+                else mbar_arrive(bar_tempty + 8 * as);
+            }
+            if (++as == ACC_STAGES) { as = 0; aphase ^= 1; }
+        }
+        // flush: final prune of every row, write the slot's candidate list
+        __syncwarp();
+        for (int r = 0; r < 32; ++r) {
+            const int c = __shfl_sync(FULL, cnt, r);
+            int nc; float nt;
+            const uint64_t m = warp_prune(rows + r * CAP, c, lane, nc, nt);
+            const int64_t q = q0 + quarter * 32 + r;
+            if (q < nq) partials[(q * slots + slot) * KP + lane] = m;
+        }
+    }
+
+    // ---- teardown ----
+    tc_fence_before();
+    if (CG == 2) cluster_sync_all(); else __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc<CG>(tmem_base, 512);
+    }
+}
+
+int scan_tc_slots(int64_t nq, int64_t nslots, int cg, int ctas) {
+    const int64_t rows_per_unit = (int64_t)BM * cg;
+    const int64_t groups = (nq + rows_per_unit - 1) / rows_per_unit;
+    const int64_t units = ctas / cg;
+    const int64_t ntiles = (nslots + BN - 1) / BN;
+    int64_t s = units / groups;
+    if (s > ntiles) s = ntiles;
+    if (s < 1) s = 1;
+    return (int)s;
+}
+
+cudaError_t scan_tc_init() {
+    cudaError_t e = cudaFuncSetAttribute(scan_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<1>::SMEM);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(scan_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<2>::SMEM);
+}
+
+cudaError_t launch_scan_tc(const ScanArgs& a, const CUtensorMap* map_q, const CUtensorMap* map_c,
+                           int cg, int ctas, cudaStream_t st) {
+    (void)ctas;
+    const int rows_per_unit = BM * cg;
+    const int groups = (int)((a.nq + rows_per_unit - 1) / rows_per_unit);
+    const int units = groups * a.slots;
+    const int kblocks = a.ld / BK;
+    cudaLaunchConfig_t cfg{};
+    cfg.blockDim = dim3(256);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    if (cg == 1) {
+        cfg.gridDim = dim3(units);
+        cfg.dynamicSmemBytes = TcCfg<1>::SMEM;
+        cfg.numAttrs = 0;
+        return cudaLaunchKernelEx(&cfg, scan_tc_kernel<1>, *map_q, *map_c, a.scale, a.partials, a.nq,
+                                  a.nslots, a.capacity, a.head, kblocks, a.slots, groups);
+    }
+    cfg.gridDim = dim3(units * 2);
+    cfg.dynamicSmemBytes = TcCfg<2>::SMEM;
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, scan_tc_kernel<2>, *map_q, *map_c, a.scale, a.partials, a.nq,
+                              a.nslots, a.capacity, a.head, kblocks, a.slots, groups);
+}
+
+}  // namespace pilott
