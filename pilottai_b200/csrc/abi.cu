@@ -123,6 +123,7 @@ struct pilott_mem {
     bool tc_ok = false;
     int opt_kernel = 0;     // 0 auto, 1 generic, 2 tc 1-CTA, 3 tc pair
     int opt_ctas = 0;
+    int opt_dbg = 0;
     int64_t launches = 0;
 };
 
@@ -185,7 +186,9 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
     pilott::ScanArgs a{};
     a.qb = h->qbuf.p; a.vec = h->vec; a.scale = h->scale; a.nq = nq;
     a.nslots = h->count; a.capacity = h->capacity; a.head = h->head; a.ld = h->ld;
+    a.dbg = h->opt_dbg;
     CUtensorMap map_q, map_c;
+    int lists = 0;
     if (kern != 1) {
         const int cg = kern == 3 ? 2 : 1;
         rc = encode_map(&map_q, h->qbuf.p, nq, h->ld, 128);
@@ -193,20 +196,22 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
         if (cg == 1) map_c = h->map_c;
         else { rc = encode_map(&map_c, h->vec, h->capacity, h->ld, 128); if (rc) return rc; }
         a.slots = pilott::scan_tc_slots(nq, h->count, cg, ctas);
-        rc = h->partials.ensure((size_t)nq * a.slots * KP_HOST * 8);
+        lists = a.slots * pilott::scan_tc_lists_per_slot();
+        rc = h->partials.ensure((size_t)nq * lists * KP_HOST * 8);
         if (rc) return rc;
         a.partials = (uint64_t*)h->partials.p;
         CK(pilott::launch_scan_tc(a, &map_q, &map_c, cg, ctas, st));
     } else {
         a.slots = pilott::scan_generic_slots(nq, h->count, h->num_sms);
-        rc = h->partials.ensure((size_t)nq * a.slots * KP_HOST * 8);
+        lists = a.slots;
+        rc = h->partials.ensure((size_t)nq * lists * KP_HOST * 8);
         if (rc) return rc;
         a.partials = (uint64_t*)h->partials.p;
         CK(pilott::launch_scan_generic(a, h->num_sms, st));
     }
     if (out_inexact) CK(cudaMemsetAsync(out_inexact, 0, 4, st));
     pilott::FinishArgs f{};
-    f.partials = a.partials; f.slots = a.slots; f.qb = h->qbuf.p; f.vec = h->vec; f.ld = h->ld;
+    f.partials = a.partials; f.slots = lists; f.qb = h->qbuf.p; f.vec = h->vec; f.ld = h->ld;
     f.nq = nq; f.capacity = h->capacity; f.head = h->head; f.base_seq = h->total - h->count;
     f.k = k;
     f.err = h->ld * 2.4e-7 > 1e-4 ? h->ld * 2.4e-7 : 1e-4;
@@ -336,6 +341,8 @@ int pilott_mem_set_option(pilott_mem_t* h, int which, int64_t value) {
     } else if (which == 1) {
         if (value < 0 || value > 4096) return fail(PILOTT_EINVAL, "CTA count out of range");
         h->opt_ctas = (int)value;
+    } else if (which == 2) {
+        h->opt_dbg = (int)value;      // developer switches (profiling experiments); 0 = off
     } else {
         return fail(PILOTT_EINVAL, "unknown option");
     }

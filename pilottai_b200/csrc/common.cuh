@@ -64,12 +64,25 @@ __device__ __forceinline__ uint64_t warp_min64(uint64_t v) {
     return v;
 }
 
-// Keep the KP best of a row buffer holding cnt (<= CAP) keys.  Whole warp cooperates.
-// Leaves the survivors (unsorted, empty = 0) in buf[0..KP) and returns them per lane.
-__device__ __forceinline__ uint64_t warp_prune(uint64_t* buf, int cnt, int lane, int& new_cnt,
-                                               float& new_thr) {
+// Raw candidate entry (written by the tcgen05 epilogue's append): low 32 bits = physical
+// ring slot.  Converted key: low 32 bits = 0xFFFFFFFF - age.  The conversion is deferred to
+// prune time so the hot loop does not pay for it.
+__device__ __forceinline__ uint64_t raw_to_key(uint64_t raw, uint32_t head, uint32_t cap) {
+    int32_t age = (int32_t)((uint32_t)raw - head);
+    if (age < 0) age += (int32_t)cap;
+    return (raw & 0xFFFFFFFF00000000ull) | (uint64_t)(0xFFFFFFFFu - (uint32_t)age);
+}
+
+// Keep the KP best of a row buffer holding cnt (<= CAPT <= 64) entries.  Whole warp
+// cooperates.  Entries at index >= conv are still raw.  Leaves the survivors (unsorted,
+// empty = 0) in buf[0..KP) and returns them per lane.
+template <int CAPT>
+__device__ __forceinline__ uint64_t warp_prune(uint64_t* buf, int cnt, int conv, uint32_t head,
+                                               uint32_t cap, int lane, int& new_cnt, float& new_thr) {
     uint64_t a = lane < cnt ? buf[lane] : 0ull;
-    uint64_t b = (lane + 32) < cnt ? buf[lane + 32] : 0ull;
+    uint64_t b = (CAPT > 32 && (lane + 32) < cnt) ? buf[lane + 32] : 0ull;
+    if (lane < cnt && lane >= conv) a = raw_to_key(a, head, cap);
+    if ((lane + 32) < cnt && (lane + 32) >= conv) b = raw_to_key(b, head, cap);
     a = warp_sort64<true>(a, lane);
     b = warp_sort64<false>(b, lane);
     const uint64_t m = a > b ? a : b;          // half-cleaner of a bitonic sequence: the top 32
@@ -81,18 +94,20 @@ __device__ __forceinline__ uint64_t warp_prune(uint64_t* buf, int cnt, int lane,
 }
 
 // Prune every row of this warp's 32-row group whose bit is set in `mask`.
-// rows = base of the warp's 32 row buffers (row r at rows + r*CAP).
+// rows = base of the warp's 32 row buffers (row r at rows + r*CAPT).
+template <int CAPT>
 __device__ __forceinline__ void warp_prune_rows(unsigned mask, uint64_t* rows, int lane, int& cnt,
-                                                float& thr) {
+                                                int& conv, float& thr, uint32_t head, uint32_t cap) {
     __syncwarp();
     while (mask) {
         const int r = __ffs(mask) - 1;
         mask &= mask - 1;
         const int c = __shfl_sync(FULL, cnt, r);
+        const int cv = __shfl_sync(FULL, conv, r);
         int nc;
         float nt;
-        warp_prune(rows + r * CAP, c, lane, nc, nt);
-        if (lane == r) { cnt = nc; thr = nt; }
+        warp_prune<CAPT>(rows + r * CAPT, c, cv, head, cap, lane, nc, nt);
+        if (lane == r) { cnt = nc; conv = nc; thr = nt; }
     }
     __syncwarp();
 }

@@ -17,6 +17,7 @@ struct ScanArgs {
     int64_t head;            // physical slot of the oldest row
     int ld;                  // row stride in elements (multiple of 64)
     int slots;               // partial lists per query
+    int dbg;                 // developer switches for the tcgen05 kernel (0 in production)
 };
 
 // generic CUDA-core scan (any shape).  Returns slots used via args.slots (caller sets).
@@ -27,6 +28,7 @@ int scan_generic_slots(int64_t nq, int64_t nslots, int num_sms);
 cudaError_t launch_scan_tc(const ScanArgs& a, const CUtensorMap* map_q, const CUtensorMap* map_c,
                            int cg, int ctas, cudaStream_t st);
 int scan_tc_slots(int64_t nq, int64_t nslots, int cg, int ctas);
+int scan_tc_lists_per_slot();   // candidate lists each (query, slot) writes; partials hold slots*this lists
 cudaError_t scan_tc_init();   // opt-in shared memory attributes
 
 cudaError_t launch_append(const float* x, int64_t n, int dim, int ld, void* vec, float* inv_norm,

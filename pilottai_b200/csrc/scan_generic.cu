@@ -33,7 +33,8 @@ scan_generic_kernel(const __nv_bfloat16* __restrict__ qb, const __nv_bfloat16* _
     const int64_t t_lo = ntiles * slot / slots, t_hi = ntiles * (slot + 1) / slots;
 
     float thr = -INFINITY;      // per query row (threads 0..63 own one row each)
-    int cnt = 0;
+    int cnt = 0, conv = 0;
+    const uint32_t head32 = (uint32_t)head, cap32 = (uint32_t)capacity;
     const int ty = tid >> 4, tx = tid & 15;
     const int lrow = tid >> 2, lk = (tid & 3) * 8;     // loader mapping: 64 rows x 4 chunks of 8
 
@@ -86,14 +87,11 @@ scan_generic_kernel(const __nv_bfloat16* __restrict__ qb, const __nv_bfloat16* _
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                     const float s = sm.s[tid][c0 + j];
-                    if (s >= thr) {
-                        int64_t age = n0 + c0 + j - head;
-                        if (age < 0) age += capacity;
-                        mine[cnt++] = make_key(s, (uint32_t)age);
-                    }
+                    if (s >= thr)      // raw entry: physical slot in the low word (converted at prune time)
+                        mine[cnt++] = ((uint64_t)f2ord(s) << 32) | (uint32_t)(n0 + c0 + j);
                 }
                 const unsigned full = __ballot_sync(FULL, cnt > CAP - 8);
-                if (full) warp_prune_rows(full, rows, lane, cnt, thr);
+                if (full) warp_prune_rows<CAP>(full, rows, lane, cnt, conv, thr, head32, cap32);
             }
         }
         // the next tile's first __syncthreads orders the reuse of the s tile
@@ -104,8 +102,9 @@ scan_generic_kernel(const __nv_bfloat16* __restrict__ qb, const __nv_bfloat16* _
         __syncwarp();
         for (int r = 0; r < 32; ++r) {
             const int c = __shfl_sync(FULL, cnt, r);
+            const int cv = __shfl_sync(FULL, conv, r);
             int nc; float nt;
-            const uint64_t m = warp_prune(rows + r * CAP, c, lane, nc, nt);
+            const uint64_t m = warp_prune<CAP>(rows + r * CAP, c, cv, head32, cap32, lane, nc, nt);
             const int64_t q = q0 + warp * 32 + r;
             if (q < nq) partials[(q * slots + slot) * KP + lane] = m;
         }

@@ -12,8 +12,11 @@
 // life and sweeps a contiguous range of 256-row corpus tiles ("slot"), so the selection
 // state stays on chip; the per-slot candidate lists are merged by finish.cu.
 //
-// Warp roles (256 threads): 0 = TMA producer, 1 = MMA issuer, 2 = TMEM allocator,
-// 3 = idle, 4..7 = epilogue (TMEM lane quarter = warp % 4).
+// Warp roles (384 threads): 0 = TMA producer, 1 = MMA issuer, 2 = TMEM allocator,
+// 3 = idle, 4..11 = epilogue in two sets of four warps (TMEM lane quarter = warp % 4).
+// Set s drains accumulator stage s, i.e. every other corpus tile, with its own candidate
+// buffers, so each set has two tile-times per tile and every SM sub-partition holds two
+// epilogue warps that cover each other's latencies.
 // Pipelines: smem full/empty ring (TMA <-> MMA), TMEM full/empty x2 (MMA <-> epilogue).
 #include "common.cuh"
 #include "internal.h"
@@ -26,15 +29,20 @@ constexpr int BK = 64;         // bf16 elements per k-block = one 128-byte swizz
 constexpr int UK = 16;         // UMMA K for 16-bit inputs
 constexpr int ACC_STAGES = 2;  // 2 x 256 TMEM columns
 
+constexpr int EPI_SETS = 2;    // one per accumulator stage
+constexpr int CAPT = 46;       // per-row candidate buffer: KP survivors + pending appends (smem budget)
+constexpr int TC_THREADS = 128 + EPI_SETS * 128;
+
 template <int CG> struct TcCfg {
-    static constexpr int STAGES = CG == 1 ? 3 : 4;
+    static constexpr int STAGES = CG == 1 ? 2 : 4;
     static constexpr int A_BYTES = BM * BK * 2;                    // 16 KB
     static constexpr int B_ROWS = BN / CG;                         // rows of B this CTA loads
     static constexpr int B_BYTES = B_ROWS * BK * 2;                // 32 KB / 16 KB
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int BUF_BYTES = BM * CAP * 8;                 // 64 KB candidate buffers
+    static constexpr int BUF_BYTES = EPI_SETS * BM * CAPT * 8;     // 96 KB candidate buffers
+    static constexpr int SC_BYTES = EPI_SETS * 2 * BN * 4;         // staged scale tiles (double buffered)
     static constexpr int BAR_BYTES = 256;
-    static constexpr int SMEM = 1024 /*align slack*/ + STAGES * STAGE_BYTES + BUF_BYTES + BAR_BYTES;
+    static constexpr int SMEM = 1024 /*align slack*/ + STAGES * STAGE_BYTES + BUF_BYTES + SC_BYTES + BAR_BYTES;
 };
 
 // ---- PTX wrappers ----------------------------------------------------------------------
@@ -152,24 +160,19 @@ __host__ __device__ constexpr uint32_t make_idesc(int m, int n) {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+__device__ __forceinline__ void tmem_ld16_issue(uint32_t taddr, uint32_t (&v)[16]) {
     asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
-          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
-          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
         : "r"(taddr) : "memory");
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
-__device__ __forceinline__ float4 ldg_nc_f4(const float* p) {
-    float4 r;
-    asm volatile("ld.global.nc.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
-    return r;
-}
 __device__ __forceinline__ uint32_t cluster_ctarank() {
     uint32_t r;
     asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
@@ -184,17 +187,18 @@ __device__ __forceinline__ void cluster_sync_all() {
 // Grid: `units` work units (CTAs for CG=1, CTA pairs for CG=2).  Unit u serves query group
 // u % groups (BM*CG query rows) and slot u / groups of that group.
 template <int CG>
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(TC_THREADS, 1)
 scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_c,
                const float* __restrict__ scale, uint64_t* __restrict__ partials, int64_t nq,
-               int64_t nslots, int64_t capacity, int64_t head, int kblocks, int slots, int groups) {
+               int64_t nslots, int64_t capacity, int64_t head, int kblocks, int slots, int groups, int dbg) {
     using Cfg = TcCfg<CG>;
     extern __shared__ unsigned char smem_dyn[];
     const uint32_t base = (smem_u32(smem_dyn) + 1023u) & ~1023u;        // 1024-B aligned (swizzle atom)
     unsigned char* base_ptr = smem_dyn + (base - smem_u32(smem_dyn));
     const uint32_t stage_base = base;
     uint64_t* bufs = reinterpret_cast<uint64_t*>(base_ptr + Cfg::STAGES * Cfg::STAGE_BYTES);
-    const uint32_t bar_base = base + Cfg::STAGES * Cfg::STAGE_BYTES + Cfg::BUF_BYTES;
+    float* ssc = reinterpret_cast<float*>(base_ptr + Cfg::STAGES * Cfg::STAGE_BYTES + Cfg::BUF_BYTES);
+    const uint32_t bar_base = base + Cfg::STAGES * Cfg::STAGE_BYTES + Cfg::BUF_BYTES + Cfg::SC_BYTES;
     // barrier layout (8 B each): full[STAGES], empty[STAGES], tfull[2], tempty[2], then tmem ptr
     const uint32_t bar_full = bar_base;
     const uint32_t bar_empty = bar_base + 8 * Cfg::STAGES;
@@ -202,7 +206,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
     const uint32_t bar_tempty = bar_tfull + 8 * ACC_STAGES;
     const uint32_t tmem_slot = bar_tempty + 8 * ACC_STAGES;
     volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(
-        base_ptr + Cfg::STAGES * Cfg::STAGE_BYTES + Cfg::BUF_BYTES + 16 * Cfg::STAGES + 16 * ACC_STAGES);
+        base_ptr + Cfg::STAGES * Cfg::STAGE_BYTES + Cfg::BUF_BYTES + Cfg::SC_BYTES + 16 * Cfg::STAGES + 16 * ACC_STAGES);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = CG == 2 ? cluster_ctarank() : 0u;
@@ -289,58 +293,89 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
         __syncwarp();
     } else if (warp >= 4) {
         // ===== epilogue: scale, threshold, append, prune =====
+        const int set = (warp - 4) >> 2;                           // accumulator stage this set drains
         const int quarter = warp & 3;                              // TMEM lanes [32*quarter, +32)
         const int row = quarter * 32 + lane;                       // query row within the CTA tile
-        uint64_t* rows = bufs + (size_t)quarter * 32 * CAP;
-        uint64_t* mine = bufs + (size_t)row * CAP;
+        const int tis = row;                                       // thread index within the set
+        uint64_t* rows = bufs + ((size_t)set * BM + quarter * 32) * CAPT;
+        uint64_t* mine = bufs + ((size_t)set * BM + row) * CAPT;
+        float* sc_set = ssc + set * 2 * BN;                        // two staged scale tiles
+        const uint32_t head32 = (uint32_t)head, cap32 = (uint32_t)capacity;
         float thr = -INFINITY;
-        int cnt = 0;
-        int as = 0; uint32_t aphase = 0;
-        for (int64_t t = t_lo; t < t_hi; ++t) {
-            const int64_t n0 = t * BN;
-            mbar_wait(bar_tfull + 8 * as, aphase);
+        int cnt = 0, conv = 0;
+        uint32_t aphase = 0;
+        int sbuf = 0;
+        // stage the first tile's scale row: 2 floats per thread, coalesced
+        if (t_lo + set < t_hi) {
+            const float2 s2 = __ldg(reinterpret_cast<const float2*>(scale + (t_lo + set) * BN) + tis);
+            reinterpret_cast<float2*>(sc_set)[tis] = s2;
+        }
+        named_bar_sync(1 + set, 128);
+        for (int64_t t = t_lo + set; t < t_hi; t += EPI_SETS) {
+            const uint32_t n0 = (uint32_t)(t * BN);
+            // prefetch the next tile's scale row into registers; parked in smem at the end
+            float2 nxt = make_float2(0.f, 0.f);
+            const bool has_next = t + EPI_SETS < t_hi;
+            if (has_next) nxt = __ldg(reinterpret_cast<const float2*>(scale + (t + EPI_SETS) * BN) + tis);
+            const float* scb = sc_set + sbuf * BN;
+            mbar_wait(bar_tfull + 8 * set, aphase);
             tc_fence_after();
-            const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
+            const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + set * BN;
 #pragma unroll 1
-            for (int c = 0; c < BN; c += 32) {
-                uint32_t v[32];
-                tmem_ld32(taddr0 + c, v);
-                const float* sp = scale + n0 + c;
+            for (int c = 0; c < ((dbg & 1) ? 0 : BN); c += 16) {
+                uint32_t v[16];
+                tmem_ld16_issue(taddr0 + c, v);
+                float sc[16];
 #pragma unroll
-                for (int g8 = 0; g8 < 4; ++g8) {
-                    const float4 s0 = ldg_nc_f4(sp + g8 * 8);
-                    const float4 s1 = ldg_nc_f4(sp + g8 * 8 + 4);
-                    const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+                for (int j = 0; j < 4; ++j) {
+                    const float4 f = *reinterpret_cast<const float4*>(scb + c + 4 * j);   // broadcast LDS.128
+                    sc[4 * j] = f.x; sc[4 * j + 1] = f.y; sc[4 * j + 2] = f.z; sc[4 * j + 3] = f.w;
+                }
+                tmem_ld_wait();
+                if (dbg & 2) { if (v[0] == 0x7fc12345u && v[15] == 0x7fc54321u) thr = 1.f; continue; }
+#pragma unroll
+                for (int g8 = 0; g8 < 2; ++g8) {
+                    float s[8];
+                    bool hit = false;
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
-                        const float s = __uint_as_float(v[g8 * 8 + j]) * sc[j];
-                        if (s >= thr) {
-                            int64_t age = n0 + c + g8 * 8 + j - head;
-                            if (age < 0) age += capacity;
-                            mine[cnt++] = make_key(s, (uint32_t)age);
-                        }
+                        s[j] = __uint_as_float(v[g8 * 8 + j]) * sc[g8 * 8 + j];
+                        hit |= (s[j] >= thr);
                     }
-                    const unsigned full = __ballot_sync(FULL, cnt > CAP - 8);
-                    if (full) warp_prune_rows(full, rows, lane, cnt, thr);
+                    if (__any_sync(FULL, hit)) {
+                        // slow path (warp-uniform entry): append survivors, prune full rows
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            if (s[j] >= thr)
+                                mine[cnt++] = ((uint64_t)f2ord(s[j]) << 32) | (n0 + c + g8 * 8 + j);
+                        }
+                        const unsigned full = __ballot_sync(FULL, cnt > CAPT - 8);
+                        if (full) warp_prune_rows<CAPT>(full, rows, lane, cnt, conv, thr, head32, cap32);
+                    }
                 }
             }
             // release this accumulator stage to the MMA issuer (in the leader CTA)
             tc_fence_before();
             __syncwarp();
             if (lane == 0) {
-                if (CG == 2) mbar_arrive_cluster(bar_tempty + 8 * as, 0);
-                else mbar_arrive(bar_tempty + 8 * as);
+                if (CG == 2) mbar_arrive_cluster(bar_tempty + 8 * set, 0);
+                else mbar_arrive(bar_tempty + 8 * set);
             }
-            if (++as == ACC_STAGES) { as = 0; aphase ^= 1; }
+            aphase ^= 1;
+            // park the prefetched scale row in the other staging buffer (last read one tile ago)
+            sbuf ^= 1;
+            if (has_next) reinterpret_cast<float2*>(sc_set + sbuf * BN)[tis] = nxt;
+            named_bar_sync(1 + set, 128);
         }
-        // flush: final prune of every row, write the slot's candidate list
+        // flush: final prune of every row, write this (slot, set) candidate list
         __syncwarp();
         for (int r = 0; r < 32; ++r) {
             const int c = __shfl_sync(FULL, cnt, r);
+            const int cv = __shfl_sync(FULL, conv, r);
             int nc; float nt;
-            const uint64_t m = warp_prune(rows + r * CAP, c, lane, nc, nt);
+            const uint64_t m = warp_prune<CAPT>(rows + r * CAPT, c, cv, head32, cap32, lane, nc, nt);
             const int64_t q = q0 + quarter * 32 + r;
-            if (q < nq) partials[(q * slots + slot) * KP + lane] = m;
+            if (q < nq) partials[(q * (slots * EPI_SETS) + slot * EPI_SETS + set) * KP + lane] = m;
         }
     }
 
@@ -352,6 +387,8 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
         tmem_dealloc<CG>(tmem_base, 512);
     }
 }
+
+int scan_tc_lists_per_slot() { return EPI_SETS; }
 
 int scan_tc_slots(int64_t nq, int64_t nslots, int cg, int ctas) {
     const int64_t rows_per_unit = (int64_t)BM * cg;
@@ -378,7 +415,7 @@ cudaError_t launch_scan_tc(const ScanArgs& a, const CUtensorMap* map_q, const CU
     const int units = groups * a.slots;
     const int kblocks = a.ld / BK;
     cudaLaunchConfig_t cfg{};
-    cfg.blockDim = dim3(256);
+    cfg.blockDim = dim3(TC_THREADS);
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
     if (cg == 1) {
@@ -386,7 +423,7 @@ cudaError_t launch_scan_tc(const ScanArgs& a, const CUtensorMap* map_q, const CU
         cfg.dynamicSmemBytes = TcCfg<1>::SMEM;
         cfg.numAttrs = 0;
         return cudaLaunchKernelEx(&cfg, scan_tc_kernel<1>, *map_q, *map_c, a.scale, a.partials, a.nq,
-                                  a.nslots, a.capacity, a.head, kblocks, a.slots, groups);
+                                  a.nslots, a.capacity, a.head, kblocks, a.slots, groups, a.dbg);
     }
     cfg.gridDim = dim3(units * 2);
     cfg.dynamicSmemBytes = TcCfg<2>::SMEM;
@@ -394,7 +431,9 @@ cudaError_t launch_scan_tc(const ScanArgs& a, const CUtensorMap* map_q, const CU
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
     return cudaLaunchKernelEx(&cfg, scan_tc_kernel<2>, *map_q, *map_c, a.scale, a.partials, a.nq,
-                              a.nslots, a.capacity, a.head, kblocks, a.slots, groups);
+                              a.nslots, a.capacity, a.head, kblocks, a.slots, groups, a.dbg);
 }
 
 }  // namespace pilott
+
+static_assert(pilott::TcCfg<1>::SMEM <= 232448 && pilott::TcCfg<2>::SMEM <= 232448, "shared memory budget (227 KB per CTA)");

@@ -1,0 +1,267 @@
+"""EnhancedMemory -- drop-in for pilott.memory.enhanced_memory.EnhancedMemory whose
+semantic store lives on a B200.
+
+Same class name, constructor, coroutines, argument meaning and error behaviour as the
+reference (pilott/memory/enhanced_memory.py); written from scratch.  What changes:
+
+* ``semantic_search`` ranks by cosine similarity of embeddings on the GPU instead of the
+  reference's case-insensitive substring test (:110), and returns the ``limit`` BEST
+  matches rather than the first ``limit`` found (:111-113).
+* keyword-only extras: ``embedding=`` / ``query_embedding=`` / ``order=`` and the batched
+  ``store_semantic_batch`` / ``semantic_search_batch``.
+* reference defects deliberately NOT reproduced: stale tag/priority
+  indexes after the deque overflows (:86-87 vs :133-144), ``max()`` of an empty index on
+  an empty store (:124), first-found early break.
+
+Host side keeps the ``MemoryItem`` objects (text, metadata) in insertion order; the device
+keeps one row per item (bf16 vector, inverse norm, priority, tag mask, expiry).  The two are
+joined by the insertion sequence number the search returns.
+"""
+from __future__ import annotations
+
+import asyncio
+from collections import deque
+from datetime import datetime, timedelta
+from typing import Any, Dict, Iterable, List, Optional, Sequence, Set, Tuple
+
+import numpy as np
+from pydantic import BaseModel, ConfigDict, Field
+
+from ._lib import MAX_TAGS
+from .embedder import HashEmbedder
+from .store import SemanticStore
+
+_EPOCH = datetime(1970, 1, 1)
+
+
+def _to_us(t: datetime) -> int:
+    """Naive local datetime -> integer microseconds (monotone, exact)."""
+    d = t - _EPOCH
+    return (d.days * 86400 + d.seconds) * 1_000_000 + d.microseconds
+
+
+class MemoryItem(BaseModel):
+    """One stored memory (field-compatible with the reference's MemoryItem, :9-21)."""
+    model_config = ConfigDict(arbitrary_types_allowed=True)
+    text: str
+    metadata: Dict[str, Any] = Field(default_factory=dict)
+    timestamp: datetime = Field(default_factory=datetime.now)
+    tags: Set[str] = Field(default_factory=set)
+    priority: int = Field(ge=0, default=0)
+    expires_at: Optional[datetime] = None
+    version: int = 1
+
+    def is_expired(self) -> bool:
+        return bool(self.expires_at and datetime.now() > self.expires_at)
+
+
+class EnhancedMemory:
+    def __init__(self, max_size: int = 10000, cleanup_interval: int = 3600, *, dim: int = 768,
+                 device: int = 0, embedder=None):
+        self.max_size = int(max_size)
+        self.dim = int(dim)
+        self._items: deque = deque(maxlen=self.max_size)       # MemoryItem, oldest first
+        self._store = SemanticStore(self.dim, self.max_size, device)
+        self._embed = embedder or HashEmbedder(self.dim)
+        self._tag_bits: Dict[str, int] = {}
+        self._task_history: Dict[str, deque] = {}
+        self._agent_interactions: Dict[str, Dict[str, Any]] = {}
+        self._pattern_store: Dict[str, Dict[str, Any]] = {}
+        self.max_task_history = 1000
+        self.cleanup_interval = cleanup_interval
+        self.last_cleanup = datetime.now()
+        self._semantic_lock = asyncio.Lock()
+        self._task_lock = asyncio.Lock()
+        self._interaction_lock = asyncio.Lock()
+        self._pattern_lock = asyncio.Lock()
+        self._cleanup_task = None
+
+    # ---- lifecycle (reference :49-58) ---------------------------------------------------
+    async def start(self):
+        self._cleanup_task = asyncio.create_task(self._periodic_cleanup())
+
+    async def stop(self):
+        if self._cleanup_task:
+            self._cleanup_task.cancel()
+            try:
+                await self._cleanup_task
+            except asyncio.CancelledError:
+                pass
+
+    def close(self):
+        self._store.close()
+
+    # ---- tags -> bits ---------------------------------------------------------------------
+    def _mask_for_store(self, tags: Iterable[str]) -> int:
+        m = 0
+        for t in tags:
+            b = self._tag_bits.get(t)
+            if b is None:
+                if len(self._tag_bits) >= MAX_TAGS:
+                    raise ValueError(f"more than {MAX_TAGS} distinct tags")
+                b = self._tag_bits[t] = len(self._tag_bits)
+            m |= 1 << b
+        return m
+
+    def _mask_for_query(self, tags: Optional[Iterable[str]]) -> Optional[int]:
+        """None when some requested tag was never stored: no row can match (:126-130)."""
+        m = 0
+        for t in tags or ():
+            b = self._tag_bits.get(t)
+            if b is None:
+                return None
+            m |= 1 << b
+        return m
+
+    # ---- store (reference :60-91) ---------------------------------------------------------
+    async def store_semantic(self, text: str, metadata: Optional[Dict[str, Any]] = None,
+                             tags: Optional[Set[str]] = None, priority: int = 0,
+                             ttl: Optional[int] = None, *, embedding=None) -> None:
+        if not text:
+            raise ValueError("Text cannot be empty")
+        try:
+            await self.store_semantic_batch([text], None if embedding is None else np.asarray(embedding)[None],
+                                            metadata=[metadata], tags=[tags], priority=[priority], ttl=[ttl])
+        except Exception as e:
+            raise ValueError(f"Failed to store content: {str(e)}")
+
+    async def store_semantic_batch(self, texts: Sequence[str], embeddings=None, *, metadata=None, tags=None,
+                                   priority=None, ttl=None) -> int:
+        """Append len(texts) items in one device call.  Returns the first sequence number."""
+        n = len(texts)
+        if any(not t for t in texts):
+            raise ValueError("Text cannot be empty")
+        now = datetime.now()
+        items = []
+        for i in range(n):
+            t = None if ttl is None else ttl[i]
+            items.append(MemoryItem(
+                text=texts[i], metadata=(metadata[i] if metadata else None) or {},
+                tags=(tags[i] if tags else None) or set(),
+                priority=(priority[i] if priority is not None else 0),
+                expires_at=(now + timedelta(seconds=t)) if t is not None else None))
+        if embeddings is None:
+            embeddings = self._embed.batch(list(texts))
+        emb = np.ascontiguousarray(embeddings, dtype=np.float32).reshape(n, self.dim)
+        prio = np.array([it.priority for it in items], dtype=np.int32)
+        exp = np.array([_to_us(it.expires_at) if it.expires_at else 0 for it in items], dtype=np.int64)
+        async with self._semantic_lock:
+            mask = np.array([self._mask_for_store(it.tags) for it in items], dtype=np.uint64)
+            first = -1
+            for lo in range(0, n, self.max_size):          # a device batch may not exceed the ring
+                hi = min(n, lo + self.max_size)
+                s = await asyncio.to_thread(self._store.append, emb[lo:hi], prio[lo:hi], mask[lo:hi], exp[lo:hi])
+                first = s if first < 0 else first
+                self._items.extend(items[lo:hi])
+        return first
+
+    # ---- search (reference :93-131) -------------------------------------------------------
+    def _item_for_seq(self, seq: int) -> MemoryItem:
+        base = self._store.total - len(self._items)
+        return self._items[seq - base]
+
+    async def semantic_search_batch(self, queries, k: int = 5, tags: Optional[Set[str]] = None,
+                                    min_priority: int = 0) -> Tuple[np.ndarray, np.ndarray]:
+        """queries [Q, dim] fp32 -> (insertion sequence numbers [Q,k] (-1 = none), scores [Q,k])."""
+        q = np.ascontiguousarray(queries, dtype=np.float32).reshape(-1, self.dim)
+        req = self._mask_for_query(tags)
+        if req is None:
+            return (np.full((q.shape[0], k), -1, np.int64), np.full((q.shape[0], k), -np.inf, np.float32))
+        async with self._semantic_lock:
+            now_us = _to_us(datetime.now())
+            return await asyncio.to_thread(self._store.search, q, k, min_priority, req, now_us)
+
+    async def semantic_search(self, query: str, tags: Optional[Set[str]] = None, min_priority: int = 0,
+                              limit: int = 5, *, query_embedding=None, order: str = "priority") -> List[MemoryItem]:
+        if not query:
+            raise ValueError("Query cannot be empty")
+        try:
+            if limit < 1:
+                return []
+            q = self._embed(query) if query_embedding is None else np.asarray(query_embedding, np.float32)
+            idx, _ = await self.semantic_search_batch(q[None], limit, tags, min_priority)
+            found = [self._item_for_seq(int(s)) for s in idx[0] if s >= 0]
+            if order == "score":
+                return found
+            return sorted(found, key=lambda x: (-x.priority, x.timestamp))       # reference :114
+        except Exception as e:
+            raise ValueError(f"Search failed: {str(e)}")
+
+    # ---- task history / interactions / patterns: host-only, same contracts (:146-246) ------
+    async def store_task(self, task_id: str, task_data: Dict[str, Any]) -> None:
+        if not task_id or not task_data:
+            raise ValueError("Task ID and data required")
+        async with self._task_lock:
+            hist = self._task_history.setdefault(task_id, deque(maxlen=self.max_task_history))
+            hist.append({"data": dict(task_data), "timestamp": datetime.now(), "version": len(hist) + 1})
+
+    async def store_interaction(self, agent_id: str, interaction_type: str, data: Dict[str, Any]) -> None:
+        if not agent_id or not interaction_type or not data:
+            raise ValueError("Agent ID, interaction type, and data required")
+        async with self._interaction_lock:
+            log = self._agent_interactions.setdefault(agent_id, {})
+            ts = datetime.now()
+            log[ts.isoformat()] = {"type": interaction_type, "data": dict(data), "timestamp": ts,
+                                   "version": len(log) + 1}
+
+    async def store_pattern(self, name: str, data: Any, ttl: Optional[int] = None) -> None:
+        if not name:
+            raise ValueError("Pattern name required")
+        async with self._pattern_lock:
+            now = datetime.now()
+            self._pattern_store[name] = {"data": data, "timestamp": now,
+                                         "expires_at": now + timedelta(seconds=ttl) if ttl is not None else None}
+
+    async def get_pattern(self, name: str) -> Optional[Any]:
+        if not name:
+            raise ValueError("Pattern name required")
+        async with self._pattern_lock:
+            p = self._pattern_store.get(name)
+            if p is None:
+                return None
+            if p["expires_at"] and datetime.now() > p["expires_at"]:
+                del self._pattern_store[name]
+                return None
+            return p["data"]
+
+    async def get_recent_tasks(self, limit: int = 10, task_type: Optional[str] = None) -> List[Dict[str, Any]]:
+        if limit < 1:
+            raise ValueError("Limit must be positive")
+        async with self._task_lock:
+            rows = [e for h in self._task_history.values() for e in h
+                    if not task_type or e["data"].get("type") == task_type]
+            return sorted(rows, key=lambda x: x["timestamp"], reverse=True)[:limit]
+
+    # ---- cleanup (reference :248-292) -----------------------------------------------------
+    async def _periodic_cleanup(self):
+        while True:
+            try:
+                await asyncio.sleep(self.cleanup_interval)
+                await self.cleanup()
+            except asyncio.CancelledError:
+                break
+            except Exception as e:                                  # pragma: no cover
+                print(f"Periodic cleanup error: {str(e)}")
+
+    async def cleanup(self):
+        try:
+            async with self._semantic_lock, self._pattern_lock:
+                now = datetime.now()
+                kept, keep = await asyncio.to_thread(self._store.compact, _to_us(now))
+                self._items = deque((it for it, k in zip(self._items, keep) if k), maxlen=self.max_size)
+                for name in [n for n, p in self._pattern_store.items() if p["expires_at"] and now > p["expires_at"]]:
+                    del self._pattern_store[name]
+            self.last_cleanup = datetime.now()
+        except Exception as e:
+            raise ValueError(f"Cleanup failed: {str(e)}")
+
+    def clear(self) -> None:
+        self._items.clear()
+        self._store.clear()
+        self._tag_bits.clear()
+        self._task_history.clear()
+        self._agent_interactions.clear()
+        self._pattern_store.clear()
+
+    def __len__(self) -> int:
+        return len(self._items)

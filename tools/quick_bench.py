@@ -31,6 +31,10 @@ inex = torch.zeros(1, dtype=torch.int32, device=dev); flags = torch.empty(nq, dt
 ref = None
 for kern in kernels:
     try:
+        dbg = 0
+        if ":" in kern:
+            kern, dbg = kern.split(":"); dbg = int(dbg)
+        st.set_debug(dbg)
         st.set_kernel(kern)
         for _ in range(2):
             st.search_into(q, k, idx, sc, sc64, inex, flags)
@@ -45,7 +49,7 @@ for kern in kernels:
         same = "" if ref is None else f" same_as_{kernels[0]}={bool((idx == ref).all())}"
         if ref is None:
             ref = idx.clone()
-        print(f"{kern:8s}: {ms:8.3f} ms/batch  {nq/(ms*1e-3):12.0f} q/s  {tf:7.1f} TFLOP/s  inexact={int(inex.item())}{same}", flush=True)
+        print(f"{kern:8s} dbg={dbg}: {ms:8.3f} ms/batch  {nq/(ms*1e-3):12.0f} q/s  {tf:7.1f} TFLOP/s  inexact={int(inex.item())}{same}", flush=True)
     except Exception as ex:
         print(f"{kern}: FAILED {ex}", flush=True)
         break
