@@ -54,7 +54,9 @@ int pilott_mem_clear(pilott_mem_t* h, void* stream);
 int pilott_mem_info(const pilott_mem_t* h, int64_t* total, int64_t* count, int64_t* capacity,
                     int* dim, int* row_stride);
 /* which = 0: scan kernel (0 auto, 1 generic CUDA-core, 2 tcgen05 1-CTA, 3 tcgen05 CTA-pair).
- * which = 1: CTAs used by the scan (0 = one per SM). */
+ * which = 1: CTAs used by the scan (0 = one per SM).
+ * which = 2: developer switches (0 in production).
+ * which = 3: candidates each partial list keeps: 0 auto (16 when k <= 12, else 32), 16, 32. */
 int pilott_mem_set_option(pilott_mem_t* h, int which, int64_t value);
 /* Kernel launches enqueued by this handle since creation (bench bookkeeping). */
 int64_t pilott_mem_launch_count(const pilott_mem_t* h);

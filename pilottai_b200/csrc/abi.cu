@@ -116,7 +116,7 @@ struct pilott_mem {
     uint64_t* tagmask = nullptr;
     int64_t* expires = nullptr;
     float* scale = nullptr;
-    DevBuf qbuf, partials, exact_scratch, stage_dev, result_dev, misc_dev;
+    DevBuf qbuf, partials, gthr, exact_scratch, stage_dev, result_dev, misc_dev;
     HostBuf stage_host;
     cudaStream_t own_stream = nullptr;
     CUtensorMap map_c;
@@ -124,6 +124,7 @@ struct pilott_mem {
     int opt_kernel = 0;     // 0 auto, 1 generic, 2 tc 1-CTA, 3 tc pair
     int opt_ctas = 0;
     int opt_dbg = 0;
+    int opt_list_len = 0;   // 0 auto (16 when k <= 12), 16, 32
     int64_t launches = 0;
 };
 
@@ -189,6 +190,7 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
     a.dbg = h->opt_dbg;
     CUtensorMap map_q, map_c;
     int lists = 0;
+    a.list_len = 32;
     if (kern != 1) {
         const int cg = kern == 3 ? 2 : 1;
         rc = encode_map(&map_q, h->qbuf.p, nq, h->ld, 128);
@@ -196,10 +198,15 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
         if (cg == 1) map_c = h->map_c;
         else { rc = encode_map(&map_c, h->vec, h->capacity, h->ld, 128); if (rc) return rc; }
         a.slots = pilott::scan_tc_slots(nq, h->count, cg, ctas);
+        a.list_len = (h->opt_list_len == 16 || (h->opt_list_len == 0 && k <= 12)) ? 16 : 32;
         lists = a.slots * pilott::scan_tc_lists_per_slot();
         rc = h->partials.ensure((size_t)nq * lists * KP_HOST * 8);
         if (rc) return rc;
         a.partials = (uint64_t*)h->partials.p;
+        rc = h->gthr.ensure((size_t)nq * 4);
+        if (rc) return rc;
+        a.gthr = (uint32_t*)h->gthr.p;
+        CK(cudaMemsetAsync(a.gthr, 0, (size_t)nq * 4, st));
         CK(pilott::launch_scan_tc(a, &map_q, &map_c, cg, ctas, st));
     } else {
         a.slots = pilott::scan_generic_slots(nq, h->count, h->num_sms);
@@ -211,7 +218,7 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
     }
     if (out_inexact) CK(cudaMemsetAsync(out_inexact, 0, 4, st));
     pilott::FinishArgs f{};
-    f.partials = a.partials; f.slots = lists; f.qb = h->qbuf.p; f.vec = h->vec; f.ld = h->ld;
+    f.partials = a.partials; f.slots = lists; f.list_len = a.list_len; f.qb = h->qbuf.p; f.vec = h->vec; f.ld = h->ld;
     f.nq = nq; f.capacity = h->capacity; f.head = h->head; f.base_seq = h->total - h->count;
     f.k = k;
     f.err = h->ld * 2.4e-7 > 1e-4 ? h->ld * 2.4e-7 : 1e-4;
@@ -307,7 +314,7 @@ int pilott_mem_destroy(pilott_mem_t* h) {
     DeviceGuard g(h->device);
     cudaDeviceSynchronize();
     free_columns(h);
-    h->qbuf.release(); h->partials.release(); h->exact_scratch.release(); h->stage_dev.release();
+    h->qbuf.release(); h->partials.release(); h->gthr.release(); h->exact_scratch.release(); h->stage_dev.release();
     h->result_dev.release(); h->misc_dev.release(); h->stage_host.release();
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     delete h;
@@ -341,6 +348,9 @@ int pilott_mem_set_option(pilott_mem_t* h, int which, int64_t value) {
     } else if (which == 1) {
         if (value < 0 || value > 4096) return fail(PILOTT_EINVAL, "CTA count out of range");
         h->opt_ctas = (int)value;
+    } else if (which == 3) {
+        if (value != 0 && value != 16 && value != 32) return fail(PILOTT_EINVAL, "list length must be 0, 16 or 32");
+        h->opt_list_len = (int)value;
     } else if (which == 2) {
         h->opt_dbg = (int)value;      // developer switches (profiling experiments); 0 = off
     } else {

@@ -73,10 +73,10 @@ __device__ __forceinline__ uint64_t raw_to_key(uint64_t raw, uint32_t head, uint
     return (raw & 0xFFFFFFFF00000000ull) | (uint64_t)(0xFFFFFFFFu - (uint32_t)age);
 }
 
-// Keep the KP best of a row buffer holding cnt (<= CAPT <= 64) entries.  Whole warp
-// cooperates.  Entries at index >= conv are still raw.  Leaves the survivors (unsorted,
-// empty = 0) in buf[0..KP) and returns them per lane.
-template <int CAPT>
+// Keep the KPT (16 or 32) best of a row buffer holding cnt (<= CAPT <= 64) entries.  Whole
+// warp cooperates.  Entries at index >= conv are still raw.  Leaves the survivors (unsorted,
+// empty = 0) in buf[0..KPT) and returns them per lane (lanes >= KPT return 0).
+template <int CAPT, int KPT>
 __device__ __forceinline__ uint64_t warp_prune(uint64_t* buf, int cnt, int conv, uint32_t head,
                                                uint32_t cap, int lane, int& new_cnt, float& new_thr) {
     uint64_t a = lane < cnt ? buf[lane] : 0ull;
@@ -85,17 +85,27 @@ __device__ __forceinline__ uint64_t warp_prune(uint64_t* buf, int cnt, int conv,
     if ((lane + 32) < cnt && (lane + 32) >= conv) b = raw_to_key(b, head, cap);
     a = warp_sort64<true>(a, lane);
     b = warp_sort64<false>(b, lane);
-    const uint64_t m = a > b ? a : b;          // half-cleaner of a bitonic sequence: the top 32
-    const uint64_t mn = warp_min64(m);
-    buf[lane] = m;
-    new_cnt = cnt < KP ? cnt : KP;
-    new_thr = cnt >= KP ? key_score(mn) : -INFINITY;
+    uint64_t m = a > b ? a : b;                // half-cleaner of a bitonic sequence: the top 32
+    if (KPT == 16) {                           // one more half-cleaner step: top 16 in lanes 0..15
+        const uint64_t o = shfl_xor64(m, 16);
+        m = (lane < 16) ? (m > o ? m : o) : 0ull;
+    }
+    uint64_t mn = m;
+#pragma unroll
+    for (int j = KPT / 2; j > 0; j >>= 1) {
+        const uint64_t o = shfl_xor64(mn, j);
+        mn = mn < o ? mn : o;
+    }
+    mn = shfl64(mn, 0);
+    if (lane < KPT) buf[lane] = m;
+    new_cnt = cnt < KPT ? cnt : KPT;
+    new_thr = cnt >= KPT ? key_score(mn) : -INFINITY;
     return m;
 }
 
 // Prune every row of this warp's 32-row group whose bit is set in `mask`.
 // rows = base of the warp's 32 row buffers (row r at rows + r*CAPT).
-template <int CAPT>
+template <int CAPT, int KPT>
 __device__ __forceinline__ void warp_prune_rows(unsigned mask, uint64_t* rows, int lane, int& cnt,
                                                 int& conv, float& thr, uint32_t head, uint32_t cap) {
     __syncwarp();
@@ -106,7 +116,7 @@ __device__ __forceinline__ void warp_prune_rows(unsigned mask, uint64_t* rows, i
         const int cv = __shfl_sync(FULL, conv, r);
         int nc;
         float nt;
-        warp_prune<CAPT>(rows + r * CAPT, c, cv, head, cap, lane, nc, nt);
+        warp_prune<CAPT, KPT>(rows + r * CAPT, c, cv, head, cap, lane, nc, nt);
         if (lane == r) { cnt = nc; conv = nc; thr = nt; }
     }
     __syncwarp();

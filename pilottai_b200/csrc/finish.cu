@@ -60,7 +60,8 @@ __device__ __forceinline__ double exact_cosine(const __nv_bfloat16* __restrict__
 
 // One warp per query.
 __global__ void __launch_bounds__(128)
-finish_kernel(const uint64_t* __restrict__ partials, int slots, const __nv_bfloat16* __restrict__ qb,
+finish_kernel(const uint64_t* __restrict__ partials, int slots, int list_len,
+              const __nv_bfloat16* __restrict__ qb,
               const __nv_bfloat16* __restrict__ vec, int ld, int64_t nq, int64_t capacity,
               int64_t head, int64_t base_seq, int k, double err, int64_t* __restrict__ out_idx,
               float* __restrict__ out_score, double* __restrict__ out_score64,
@@ -68,15 +69,33 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots, const __nv_bfloa
     const int lane = threadIdx.x & 31;
     const int64_t q = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (q >= nq) return;
-    // 1. top-KP of all slots' candidates by approximate key
-    const uint64_t* p = partials + q * slots * KP;
-    uint64_t best = warp_sort64<true>(p[lane], lane);
-    for (int s = 1; s < slots; ++s) {
-        const uint64_t x = warp_sort64<false>(p[s * KP + lane], lane);
+    // 1. top-KP of all lists' candidates by approximate key.  `bound` = best key any list may
+    //    have dropped: a FULL list (all list_len entries used) may have dropped rows no better
+    //    than its own worst entry; the merged pool, if full, dropped rows no better than its worst.
+    const int per_load = 32 / list_len;                    // lists fetched per 32-lane load (1 or 2)
+    const uint64_t* p = partials + q * (int64_t)slots * list_len;
+    const int nloads = (slots + per_load - 1) / per_load;
+    uint64_t best = 0ull, bound = 0ull;
+    for (int i = 0; i < nloads; ++i) {
+        const int li = i * per_load + lane / list_len;     // list this lane reads from
+        uint64_t x = li < slots ? p[(int64_t)li * list_len + (lane % list_len)] : 0ull;
+        uint64_t mn = x;                                   // per-list minimum (segmented butterfly)
+        for (int j = list_len / 2; j > 0; j >>= 1) {
+            const uint64_t o = shfl_xor64(mn, j);
+            mn = mn < o ? mn : o;
+        }
+        if (mn != 0ull && mn > bound) bound = mn;          // list is full: it may have dropped rows <= mn
+        x = warp_sort64<false>(x, lane);
         best = warp_sort64<true>(best > x ? best : x, lane);
     }
+#pragma unroll
+    for (int j = 16; j > 0; j >>= 1) {
+        const uint64_t o = shfl_xor64(bound, j);
+        bound = bound > o ? bound : o;
+    }
     const uint64_t worst = shfl64(best, 31);
-    const bool pool_full = worst != 0ull;                  // something may have been dropped
+    if (worst != 0ull && worst > bound) bound = worst;     // the pool itself is full
+    const bool pool_full = bound != 0ull;                  // something may have been dropped
     // 2. exact re-score
     const bool valid = best != 0ull;
     double sc = -INFINITY;
@@ -104,7 +123,7 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots, const __nv_bfloa
     if (lane == 0) {
         bool bad = false;
         if (pool_full) {
-            const double a_min = nqn > 0.0 ? (double)key_score(worst) / sqrt(nqn) : 0.0;
+            const double a_min = nqn > 0.0 ? (double)key_score(bound) / sqrt(nqn) : 0.0;
             bad = !(a_min + err < e_k);
         }
         if (flags) flags[q] = bad ? 1 : 0;
@@ -116,7 +135,7 @@ cudaError_t launch_finish(const FinishArgs& a, cudaStream_t st) {
     if (a.nq <= 0) return cudaSuccess;
     const int wpb = 4;
     finish_kernel<<<(unsigned)((a.nq + wpb - 1) / wpb), wpb * 32, 0, st>>>(
-        a.partials, a.slots, (const __nv_bfloat16*)a.qb, (const __nv_bfloat16*)a.vec, a.ld, a.nq,
+        a.partials, a.slots, a.list_len, (const __nv_bfloat16*)a.qb, (const __nv_bfloat16*)a.vec, a.ld, a.nq,
         a.capacity, a.head, a.base_seq, a.k, a.err, a.out_idx, a.out_score, a.out_score64,
         a.flags, a.inexact);
     return cudaGetLastError();

@@ -11,12 +11,14 @@ struct ScanArgs {
     const void* vec;         // bf16 [capacity, ld]
     const float* scale;      // [cap_pad]: inverse norm, NaN for masked / unused slots
     uint64_t* partials;      // [nq][slots][KP] candidate keys
+    uint32_t* gthr;          // [nq] shared per-query threshold (ordered-uint score), zeroed per search
     int64_t nq;
     int64_t nslots;          // physical slots holding rows (= min(total, capacity))
     int64_t capacity;
     int64_t head;            // physical slot of the oldest row
     int ld;                  // row stride in elements (multiple of 64)
     int slots;               // partial lists per query
+    int list_len;            // candidates per list the scan writes (16 or 32)
     int dbg;                 // developer switches for the tcgen05 kernel (0 in production)
 };
 
@@ -42,7 +44,7 @@ cudaError_t launch_scale(const float* inv_norm, const int32_t* prio, const uint6
                          uint64_t req, int64_t now_us, float* scale, cudaStream_t st);
 
 struct FinishArgs {
-    const uint64_t* partials; int slots;
+    const uint64_t* partials; int slots; int list_len;
     const void* qb; const void* vec; int ld;
     int64_t nq, capacity, head, base_seq;
     int k; double err;

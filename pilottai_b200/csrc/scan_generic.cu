@@ -91,7 +91,7 @@ scan_generic_kernel(const __nv_bfloat16* __restrict__ qb, const __nv_bfloat16* _
                         mine[cnt++] = ((uint64_t)f2ord(s) << 32) | (uint32_t)(n0 + c0 + j);
                 }
                 const unsigned full = __ballot_sync(FULL, cnt > CAP - 8);
-                if (full) warp_prune_rows<CAP>(full, rows, lane, cnt, conv, thr, head32, cap32);
+                if (full) warp_prune_rows<CAP, KP>(full, rows, lane, cnt, conv, thr, head32, cap32);
             }
         }
         // the next tile's first __syncthreads orders the reuse of the s tile
@@ -104,7 +104,7 @@ scan_generic_kernel(const __nv_bfloat16* __restrict__ qb, const __nv_bfloat16* _
             const int c = __shfl_sync(FULL, cnt, r);
             const int cv = __shfl_sync(FULL, conv, r);
             int nc; float nt;
-            const uint64_t m = warp_prune<CAP>(rows + r * CAP, c, cv, head32, cap32, lane, nc, nt);
+            const uint64_t m = warp_prune<CAP, KP>(rows + r * CAP, c, cv, head32, cap32, lane, nc, nt);
             const int64_t q = q0 + warp * 32 + r;
             if (q < nq) partials[(q * slots + slot) * KP + lane] = m;
         }

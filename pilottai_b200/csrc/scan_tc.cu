@@ -32,6 +32,7 @@ constexpr int ACC_STAGES = 2;  // 2 x 256 TMEM columns
 constexpr int EPI_SETS = 2;    // one per accumulator stage
 constexpr int CAPT = 46;       // per-row candidate buffer: KP survivors + pending appends (smem budget)
 constexpr int TC_THREADS = 128 + EPI_SETS * 128;
+constexpr int SC_RING = 4;     // staged scale tiles in flight (full/empty mbarrier pair per slot)
 
 template <int CG> struct TcCfg {
     static constexpr int STAGES = CG == 1 ? 2 : 4;
@@ -40,7 +41,7 @@ template <int CG> struct TcCfg {
     static constexpr int B_BYTES = B_ROWS * BK * 2;                // 32 KB / 16 KB
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int BUF_BYTES = EPI_SETS * BM * CAPT * 8;     // 96 KB candidate buffers
-    static constexpr int SC_BYTES = EPI_SETS * 2 * BN * 4;         // staged scale tiles (double buffered)
+    static constexpr int SC_BYTES = SC_RING * BN * 4;              // ring of staged scale tiles (TMA bulk copies)
     static constexpr int BAR_BYTES = 256;
     static constexpr int SMEM = 1024 /*align slack*/ + STAGES * STAGE_BYTES + BUF_BYTES + SC_BYTES + BAR_BYTES;
 };
@@ -83,8 +84,8 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return;
     const long long t0 = clock64();
-    while (!mbar_try_wait(bar, parity)) {
-        if (clock64() - t0 > 4000000000ll) __trap();
+    for (uint32_t spins = 1; !mbar_try_wait(bar, parity); ++spins) {
+        if ((spins & 0xFFFu) == 0 && clock64() - t0 > 4000000000ll) __trap();
     }
 }
 
@@ -98,6 +99,13 @@ __device__ __forceinline__ void tma_load_2d_cg2(uint32_t dst, const CUtensorMap*
     asm volatile(
         "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
         ::"r"(dst), "l"(map), "r"(bar_cluster), "r"(c0), "r"(c1) : "memory");
+}
+
+// 1-D bulk copy global -> shared, completion counted on a CTA-local mbarrier.
+__device__ __forceinline__ void bulk_load_1d(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+        ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
 
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -186,27 +194,30 @@ __device__ __forceinline__ void cluster_sync_all() {
 // ---- the kernel ------------------------------------------------------------------------
 // Grid: `units` work units (CTAs for CG=1, CTA pairs for CG=2).  Unit u serves query group
 // u % groups (BM*CG query rows) and slot u / groups of that group.
-template <int CG>
+template <int CG, int KPT>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_c,
-               const float* __restrict__ scale, uint64_t* __restrict__ partials, int64_t nq,
-               int64_t nslots, int64_t capacity, int64_t head, int kblocks, int slots, int groups, int dbg) {
+               const float* __restrict__ scale, uint64_t* __restrict__ partials,
+               uint32_t* __restrict__ gthr, int64_t nq, int64_t nslots, int64_t capacity, int64_t head, int kblocks, int slots, int groups, int dbg) {
     using Cfg = TcCfg<CG>;
     extern __shared__ unsigned char smem_dyn[];
     const uint32_t base = (smem_u32(smem_dyn) + 1023u) & ~1023u;        // 1024-B aligned (swizzle atom)
     unsigned char* base_ptr = smem_dyn + (base - smem_u32(smem_dyn));
     const uint32_t stage_base = base;
     uint64_t* bufs = reinterpret_cast<uint64_t*>(base_ptr + Cfg::STAGES * Cfg::STAGE_BYTES);
-    float* ssc = reinterpret_cast<float*>(base_ptr + Cfg::STAGES * Cfg::STAGE_BYTES + Cfg::BUF_BYTES);
+    const float* ssc = reinterpret_cast<const float*>(base_ptr + Cfg::STAGES * Cfg::STAGE_BYTES + Cfg::BUF_BYTES);
     const uint32_t bar_base = base + Cfg::STAGES * Cfg::STAGE_BYTES + Cfg::BUF_BYTES + Cfg::SC_BYTES;
     // barrier layout (8 B each): full[STAGES], empty[STAGES], tfull[2], tempty[2], then tmem ptr
     const uint32_t bar_full = bar_base;
     const uint32_t bar_empty = bar_base + 8 * Cfg::STAGES;
     const uint32_t bar_tfull = bar_base + 16 * Cfg::STAGES;
     const uint32_t bar_tempty = bar_tfull + 8 * ACC_STAGES;
-    const uint32_t tmem_slot = bar_tempty + 8 * ACC_STAGES;
+    const uint32_t bar_scfull = bar_tempty + 8 * ACC_STAGES;
+    const uint32_t bar_scempty = bar_scfull + 8 * SC_RING;
+    const uint32_t tmem_slot = bar_scempty + 8 * SC_RING;
     volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(
-        base_ptr + Cfg::STAGES * Cfg::STAGE_BYTES + Cfg::BUF_BYTES + Cfg::SC_BYTES + 16 * Cfg::STAGES + 16 * ACC_STAGES);
+        base_ptr + Cfg::STAGES * Cfg::STAGE_BYTES + Cfg::BUF_BYTES + Cfg::SC_BYTES + 16 * Cfg::STAGES + 16 * ACC_STAGES + 16 * SC_RING);
+    const uint32_t ssc_u32 = base + Cfg::STAGES * Cfg::STAGE_BYTES + Cfg::BUF_BYTES;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = CG == 2 ? cluster_ctarank() : 0u;
@@ -230,6 +241,10 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
             mbar_init(bar_tfull + 8 * i, 1);
             mbar_init(bar_tempty + 8 * i, 4 * CG);     // one arrive per epilogue warp per CTA
         }
+        for (int i = 0; i < SC_RING; ++i) {
+            mbar_init(bar_scfull + 8 * i, 1);
+            mbar_init(bar_scempty + 8 * i, 4);         // the four warps of the set that read the slot
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) tmem_alloc<CG>(tmem_slot, 512);
@@ -247,6 +262,14 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                 const int n0 = (int)(t * BN) + (int)rank * Cfg::B_ROWS;
                 for (int kb = 0; kb < kblocks; ++kb) {
                     mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+                    if (kb == 0) {
+                        // this tile's scale row -> ring slot (t - t_lo) % SC_RING
+                        const int64_t ti = t - t_lo;
+                        const int ss = (int)(ti % SC_RING);
+                        mbar_wait(bar_scempty + 8 * ss, (uint32_t)(((ti / SC_RING) & 1) ^ 1));
+                        mbar_arrive_expect_tx(bar_scfull + 8 * ss, BN * 4);
+                        bulk_load_1d(ssc_u32 + ss * BN * 4, scale + t * BN, BN * 4, bar_scfull + 8 * ss);
+                    }
                     const uint32_t sa = stage_base + stage * Cfg::STAGE_BYTES;
                     const uint32_t sb = sa + Cfg::A_BYTES;
                     if (CG == 1) {
@@ -296,30 +319,26 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
         const int set = (warp - 4) >> 2;                           // accumulator stage this set drains
         const int quarter = warp & 3;                              // TMEM lanes [32*quarter, +32)
         const int row = quarter * 32 + lane;                       // query row within the CTA tile
-        const int tis = row;                                       // thread index within the set
         uint64_t* rows = bufs + ((size_t)set * BM + quarter * 32) * CAPT;
         uint64_t* mine = bufs + ((size_t)set * BM + row) * CAPT;
-        float* sc_set = ssc + set * 2 * BN;                        // two staged scale tiles
         const uint32_t head32 = (uint32_t)head, cap32 = (uint32_t)capacity;
+        constexpr int GRP = KPT == 16 ? 16 : 8;                    // elements per threshold test / fullness check
         float thr = -INFINITY;
         int cnt = 0, conv = 0;
+        const int64_t qrow = q0 + row;
+        const bool has_q = qrow < nq;
         uint32_t aphase = 0;
-        int sbuf = 0;
-        // stage the first tile's scale row: 2 floats per thread, coalesced
-        if (t_lo + set < t_hi) {
-            const float2 s2 = __ldg(reinterpret_cast<const float2*>(scale + (t_lo + set) * BN) + tis);
-            reinterpret_cast<float2*>(sc_set)[tis] = s2;
-        }
-        named_bar_sync(1 + set, 128);
         for (int64_t t = t_lo + set; t < t_hi; t += EPI_SETS) {
             const uint32_t n0 = (uint32_t)(t * BN);
-            // prefetch the next tile's scale row into registers; parked in smem at the end
-            float2 nxt = make_float2(0.f, 0.f);
-            const bool has_next = t + EPI_SETS < t_hi;
-            if (has_next) nxt = __ldg(reinterpret_cast<const float2*>(scale + (t + EPI_SETS) * BN) + tis);
-            const float* scb = sc_set + sbuf * BN;
+            // Any list's KPT-th best score for this query bounds the global top-KPT from below, so
+            // all CTAs sweeping the same query share one monotone threshold through gthr[query].
+            const uint32_t g = has_q ? __ldcg(gthr + qrow) : 0u;
+            const int64_t ti = t - t_lo;
+            const float* scb = ssc + (ti % SC_RING) * BN;
+            mbar_wait(bar_scfull + 8 * (int)(ti % SC_RING), (uint32_t)((ti / SC_RING) & 1));
             mbar_wait(bar_tfull + 8 * set, aphase);
             tc_fence_after();
+            if (g > f2ord(thr)) thr = ord2f(g);
             const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + set * BN;
 #pragma unroll 1
             for (int c = 0; c < ((dbg & 1) ? 0 : BN); c += 16) {
@@ -334,23 +353,26 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                 tmem_ld_wait();
                 if (dbg & 2) { if (v[0] == 0x7fc12345u && v[15] == 0x7fc54321u) thr = 1.f; continue; }
 #pragma unroll
-                for (int g8 = 0; g8 < 2; ++g8) {
-                    float s[8];
+                for (int g0 = 0; g0 < 16; g0 += GRP) {
+                    float s[GRP];
                     bool hit = false;
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        s[j] = __uint_as_float(v[g8 * 8 + j]) * sc[g8 * 8 + j];
+                    for (int j = 0; j < GRP; ++j) {
+                        s[j] = __uint_as_float(v[g0 + j]) * sc[g0 + j];
                         hit |= (s[j] >= thr);
                     }
                     if (__any_sync(FULL, hit)) {
                         // slow path (warp-uniform entry): append survivors, prune full rows
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) {
+                        for (int j = 0; j < GRP; ++j) {
                             if (s[j] >= thr)
-                                mine[cnt++] = ((uint64_t)f2ord(s[j]) << 32) | (n0 + c + g8 * 8 + j);
+                                mine[cnt++] = ((uint64_t)f2ord(s[j]) << 32) | (n0 + c + g0 + j);
                         }
-                        const unsigned full = __ballot_sync(FULL, cnt > CAPT - 8);
-                        if (full) warp_prune_rows<CAPT>(full, rows, lane, cnt, conv, thr, head32, cap32);
+                        const unsigned full = __ballot_sync(FULL, cnt > CAPT - GRP);
+                        if (full) {
+                            warp_prune_rows<CAPT, KPT>(full, rows, lane, cnt, conv, thr, head32, cap32);
+                            if (((full >> lane) & 1u) && has_q) atomicMax(gthr + qrow, f2ord(thr));
+                        }
                     }
                 }
             }
@@ -360,12 +382,9 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
             if (lane == 0) {
                 if (CG == 2) mbar_arrive_cluster(bar_tempty + 8 * set, 0);
                 else mbar_arrive(bar_tempty + 8 * set);
+                mbar_arrive(bar_scempty + 8 * (int)(ti % SC_RING));     // scale slot may be refilled
             }
             aphase ^= 1;
-            // park the prefetched scale row in the other staging buffer (last read one tile ago)
-            sbuf ^= 1;
-            if (has_next) reinterpret_cast<float2*>(sc_set + sbuf * BN)[tis] = nxt;
-            named_bar_sync(1 + set, 128);
         }
         // flush: final prune of every row, write this (slot, set) candidate list
         __syncwarp();
@@ -373,9 +392,9 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
             const int c = __shfl_sync(FULL, cnt, r);
             const int cv = __shfl_sync(FULL, conv, r);
             int nc; float nt;
-            const uint64_t m = warp_prune<CAPT>(rows + r * CAPT, c, cv, head32, cap32, lane, nc, nt);
+            const uint64_t m = warp_prune<CAPT, KPT>(rows + r * CAPT, c, cv, head32, cap32, lane, nc, nt);
             const int64_t q = q0 + quarter * 32 + r;
-            if (q < nq) partials[(q * (slots * EPI_SETS) + slot * EPI_SETS + set) * KP + lane] = m;
+            if (q < nq && lane < KPT) partials[(q * (slots * EPI_SETS) + slot * EPI_SETS + set) * KPT + lane] = m;
         }
     }
 
@@ -401,37 +420,43 @@ int scan_tc_slots(int64_t nq, int64_t nslots, int cg, int ctas) {
     return (int)s;
 }
 
-cudaError_t scan_tc_init() {
-    cudaError_t e = cudaFuncSetAttribute(scan_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<1>::SMEM);
-    if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(scan_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<2>::SMEM);
-}
-
-cudaError_t launch_scan_tc(const ScanArgs& a, const CUtensorMap* map_q, const CUtensorMap* map_c,
-                           int cg, int ctas, cudaStream_t st) {
-    (void)ctas;
-    const int rows_per_unit = BM * cg;
+template <int CG, int KPT>
+static cudaError_t launch_one(const ScanArgs& a, const CUtensorMap* map_q, const CUtensorMap* map_c,
+                              cudaStream_t st) {
+    const int rows_per_unit = BM * CG;
     const int groups = (int)((a.nq + rows_per_unit - 1) / rows_per_unit);
     const int units = groups * a.slots;
     const int kblocks = a.ld / BK;
     cudaLaunchConfig_t cfg{};
     cfg.blockDim = dim3(TC_THREADS);
+    cfg.gridDim = dim3(units * CG);
+    cfg.dynamicSmemBytes = TcCfg<CG>::SMEM;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
-    if (cg == 1) {
-        cfg.gridDim = dim3(units);
-        cfg.dynamicSmemBytes = TcCfg<1>::SMEM;
-        cfg.numAttrs = 0;
-        return cudaLaunchKernelEx(&cfg, scan_tc_kernel<1>, *map_q, *map_c, a.scale, a.partials, a.nq,
-                                  a.nslots, a.capacity, a.head, kblocks, a.slots, groups, a.dbg);
-    }
-    cfg.gridDim = dim3(units * 2);
-    cfg.dynamicSmemBytes = TcCfg<2>::SMEM;
     attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, scan_tc_kernel<2>, *map_q, *map_c, a.scale, a.partials, a.nq,
-                              a.nslots, a.capacity, a.head, kblocks, a.slots, groups, a.dbg);
+    return cudaLaunchKernelEx(&cfg, scan_tc_kernel<CG, KPT>, *map_q, *map_c, a.scale, a.partials, a.gthr,
+                              a.nq, a.nslots, a.capacity, a.head, kblocks, a.slots, groups, a.dbg);
+}
+
+cudaError_t scan_tc_init() {
+    cudaError_t e;
+#define PILOTT_TC_ATTR(CG, KPT)                                                                     \
+    e = cudaFuncSetAttribute(scan_tc_kernel<CG, KPT>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
+                             TcCfg<CG>::SMEM);                                                      \
+    if (e != cudaSuccess) return e;
+    PILOTT_TC_ATTR(1, 16) PILOTT_TC_ATTR(1, 32) PILOTT_TC_ATTR(2, 16) PILOTT_TC_ATTR(2, 32)
+#undef PILOTT_TC_ATTR
+    return cudaSuccess;
+}
+
+// a.list_len selects how many candidates each (query, slot, set) list keeps: 16 or 32.
+cudaError_t launch_scan_tc(const ScanArgs& a, const CUtensorMap* map_q, const CUtensorMap* map_c,
+                           int cg, int ctas, cudaStream_t st) {
+    (void)ctas;
+    if (cg == 1) return a.list_len == 16 ? launch_one<1, 16>(a, map_q, map_c, st) : launch_one<1, 32>(a, map_q, map_c, st);
+    return a.list_len == 16 ? launch_one<2, 16>(a, map_q, map_c, st) : launch_one<2, 32>(a, map_q, map_c, st);
 }
 
 }  // namespace pilott

@@ -65,6 +65,9 @@ class SemanticStore:
     def set_ctas(self, n: int) -> None:
         check(self._lib.pilott_mem_set_option(self._h, 1, int(n)))
 
+    def set_list_len(self, n: int) -> None:
+        check(self._lib.pilott_mem_set_option(self._h, 3, int(n)))
+
     def set_debug(self, flags: int) -> None:
         check(self._lib.pilott_mem_set_option(self._h, 2, int(flags)))
 
