@@ -56,10 +56,16 @@ int pilott_mem_info(const pilott_mem_t* h, int64_t* total, int64_t* count, int64
 /* which = 0: scan kernel (0 auto, 1 generic CUDA-core, 2 tcgen05 1-CTA, 3 tcgen05 CTA-pair).
  * which = 1: CTAs used by the scan (0 = one per SM).
  * which = 2: developer switches (0 in production).
- * which = 3: candidates each partial list keeps: 0 auto (16 when k <= 12, else 32), 16, 32. */
+ * which = 3: candidates each partial list keeps: 0 auto (16 when k <= 12, else 32), 16, 32.
+ * which = 4: 1 = record CUDA events around the scan kernel (read with pilott_mem_profile_read).
+ * which = 5 / 6: reported index = sequence * stride (5) + offset (6); a row-sharded store that
+ *            holds global rows i with i % world == rank uses stride = world, offset = rank. */
 int pilott_mem_set_option(pilott_mem_t* h, int which, int64_t value);
 /* Kernel launches enqueued by this handle since creation (bench bookkeeping). */
 int64_t pilott_mem_launch_count(const pilott_mem_t* h);
+/* Waits for the recorded scan kernels, returns their summed device time and count since the
+ * last read (option 4 must be on), and resets the window. */
+int pilott_mem_profile_read(pilott_mem_t* h, double* scan_ms_total, int64_t* n_scans);
 
 /* Replaces EnhancedMemory.store_semantic + _update_indexes (enhanced_memory.py:60-91,
  * :133-144) for a batch of n rows: fp32 -> bf16 (RNE), fused sum of squares -> inverse

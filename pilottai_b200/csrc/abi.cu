@@ -125,6 +125,10 @@ struct pilott_mem {
     int opt_ctas = 0;
     int opt_dbg = 0;
     int opt_list_len = 0;   // 0 auto (16 when k <= 12), 16, 32
+    int64_t seq_mul = 1, seq_add = 0;   // reported index = seq * seq_mul + seq_add (row-sharded stores)
+    bool profile = false;   // record CUDA events around the scan kernel
+    std::vector<cudaEvent_t> ev;        // pairs: [2i] before, [2i+1] after
+    size_t ev_used = 0;
     int64_t launches = 0;
 };
 
@@ -161,12 +165,29 @@ int alloc_columns(pilott_mem* h) {
     return PILOTT_OK;
 }
 
+// When profiling is on: records the "before" event and hands back the "after" event to record.
+int profile_begin(pilott_mem* h, cudaStream_t st, cudaEvent_t* after) {
+    *after = nullptr;
+    if (!h->profile) return PILOTT_OK;
+    if (h->ev_used + 2 > h->ev.size()) {
+        for (int i = 0; i < 2; ++i) {
+            cudaEvent_t e;
+            CK(cudaEventCreate(&e));
+            h->ev.push_back(e);
+        }
+    }
+    CK(cudaEventRecord(h->ev[h->ev_used], st));
+    *after = h->ev[h->ev_used + 1];
+    h->ev_used += 2;
+    return PILOTT_OK;
+}
+
 // Chooses the scan kernel: 1 generic, 2 tcgen05 1-CTA, 3 tcgen05 CTA pair.
 int pick_kernel(const pilott_mem* h) {
     if (h->opt_kernel == 1) return 1;
     if (!h->tc_ok) return 1;
     if (h->opt_kernel == 2 || h->opt_kernel == 3) return h->opt_kernel;
-    return 2;
+    return 3;      // CTA-pair tcgen05 kernel: the fast path
 }
 
 int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t min_prio, uint64_t req,
@@ -207,20 +228,28 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
         if (rc) return rc;
         a.gthr = (uint32_t*)h->gthr.p;
         CK(cudaMemsetAsync(a.gthr, 0, (size_t)nq * 4, st));
+        cudaEvent_t e1 = nullptr;
+        rc = profile_begin(h, st, &e1);
+        if (rc) return rc;
         CK(pilott::launch_scan_tc(a, &map_q, &map_c, cg, ctas, st));
+        if (e1) CK(cudaEventRecord(e1, st));
     } else {
         a.slots = pilott::scan_generic_slots(nq, h->count, h->num_sms);
         lists = a.slots;
         rc = h->partials.ensure((size_t)nq * lists * KP_HOST * 8);
         if (rc) return rc;
         a.partials = (uint64_t*)h->partials.p;
+        cudaEvent_t e1 = nullptr;
+        rc = profile_begin(h, st, &e1);
+        if (rc) return rc;
         CK(pilott::launch_scan_generic(a, h->num_sms, st));
+        if (e1) CK(cudaEventRecord(e1, st));
     }
     if (out_inexact) CK(cudaMemsetAsync(out_inexact, 0, 4, st));
     pilott::FinishArgs f{};
     f.partials = a.partials; f.slots = lists; f.list_len = a.list_len; f.qb = h->qbuf.p; f.vec = h->vec; f.ld = h->ld;
     f.nq = nq; f.capacity = h->capacity; f.head = h->head; f.base_seq = h->total - h->count;
-    f.k = k;
+    f.k = k; f.seq_mul = h->seq_mul; f.seq_add = h->seq_add;
     f.err = h->ld * 2.4e-7 > 1e-4 ? h->ld * 2.4e-7 : 1e-4;
     f.out_idx = out_idx; f.out_score = out_score; f.out_score64 = out_score64;
     f.flags = out_flags; f.inexact = out_inexact;
@@ -261,7 +290,7 @@ int exact_core(pilott_mem* h, const float* q_dev, int64_t nq, const int32_t* qid
     for (int64_t lo = 0; lo < nsel; lo += chunk) {
         const int64_t n = nsel - lo < chunk ? nsel - lo : chunk;
         CK(pilott::launch_exact(h->qbuf.p, h->vec, h->ld, h->prio, h->tagmask, h->expires, h->count,
-                                h->capacity, h->head, h->total - h->count, ids_dev + lo, n, k, min_prio,
+                                h->capacity, h->head, h->total - h->count, h->seq_mul, h->seq_add, ids_dev + lo, n, k, min_prio,
                                 req, now_us, (double*)h->exact_scratch.p, out_idx, out_score,
                                 out_score64, st));
         h->launches += 2;
@@ -316,6 +345,7 @@ int pilott_mem_destroy(pilott_mem_t* h) {
     free_columns(h);
     h->qbuf.release(); h->partials.release(); h->gthr.release(); h->exact_scratch.release(); h->stage_dev.release();
     h->result_dev.release(); h->misc_dev.release(); h->stage_host.release();
+    for (cudaEvent_t e : h->ev) cudaEventDestroy(e);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     delete h;
     return PILOTT_OK;
@@ -348,6 +378,14 @@ int pilott_mem_set_option(pilott_mem_t* h, int which, int64_t value) {
     } else if (which == 1) {
         if (value < 0 || value > 4096) return fail(PILOTT_EINVAL, "CTA count out of range");
         h->opt_ctas = (int)value;
+    } else if (which == 4) {
+        h->profile = value != 0;
+    } else if (which == 5) {
+        if (value < 1) return fail(PILOTT_EINVAL, "sequence stride must be >= 1");
+        h->seq_mul = value;
+    } else if (which == 6) {
+        if (value < 0) return fail(PILOTT_EINVAL, "sequence offset must be >= 0");
+        h->seq_add = value;
     } else if (which == 3) {
         if (value != 0 && value != 16 && value != 32) return fail(PILOTT_EINVAL, "list length must be 0, 16 or 32");
         h->opt_list_len = (int)value;
@@ -360,6 +398,22 @@ int pilott_mem_set_option(pilott_mem_t* h, int which, int64_t value) {
 }
 
 int64_t pilott_mem_launch_count(const pilott_mem_t* h) { return h ? h->launches : 0; }
+
+int pilott_mem_profile_read(pilott_mem_t* h, double* scan_ms_total, int64_t* n_scans) {
+    if (!h) return fail(PILOTT_EINVAL, "handle is NULL");
+    DeviceGuard g(h->device);
+    double tot = 0.0;
+    for (size_t i = 0; i + 1 < h->ev_used; i += 2) {
+        CK(cudaEventSynchronize(h->ev[i + 1]));
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, h->ev[i], h->ev[i + 1]));
+        tot += ms;
+    }
+    if (scan_ms_total) *scan_ms_total = tot;
+    if (n_scans) *n_scans = (int64_t)(h->ev_used / 2);
+    h->ev_used = 0;
+    return PILOTT_OK;
+}
 
 int pilott_mem_append(pilott_mem_t* h, const float* x_dev, int64_t n, const int32_t* prio_dev,
                       const uint64_t* tagmask_dev, const int64_t* expires_us_dev, int64_t* first_seq,

@@ -63,7 +63,8 @@ __global__ void __launch_bounds__(128)
 finish_kernel(const uint64_t* __restrict__ partials, int slots, int list_len,
               const __nv_bfloat16* __restrict__ qb,
               const __nv_bfloat16* __restrict__ vec, int ld, int64_t nq, int64_t capacity,
-              int64_t head, int64_t base_seq, int k, double err, int64_t* __restrict__ out_idx,
+              int64_t head, int64_t base_seq, int64_t seq_mul, int64_t seq_add, int k, double err,
+              int64_t* __restrict__ out_idx,
               float* __restrict__ out_score, double* __restrict__ out_score64,
               uint8_t* __restrict__ flags, int32_t* __restrict__ inexact) {
     const int lane = threadIdx.x & 31;
@@ -113,7 +114,7 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots, int list_len,
     warp_sort_pairs(sc, seq, lane);
     if (lane < k) {
         const bool ok = seq != INT64_MAX;
-        out_idx[q * k + lane] = ok ? seq : -1;
+        out_idx[q * k + lane] = ok ? seq * seq_mul + seq_add : -1;
         out_score[q * k + lane] = ok ? (float)sc : -INFINITY;
         if (out_score64) out_score64[q * k + lane] = ok ? sc : -INFINITY;
     }
@@ -136,7 +137,7 @@ cudaError_t launch_finish(const FinishArgs& a, cudaStream_t st) {
     const int wpb = 4;
     finish_kernel<<<(unsigned)((a.nq + wpb - 1) / wpb), wpb * 32, 0, st>>>(
         a.partials, a.slots, a.list_len, (const __nv_bfloat16*)a.qb, (const __nv_bfloat16*)a.vec, a.ld, a.nq,
-        a.capacity, a.head, a.base_seq, a.k, a.err, a.out_idx, a.out_score, a.out_score64,
+        a.capacity, a.head, a.base_seq, a.seq_mul, a.seq_add, a.k, a.err, a.out_idx, a.out_score, a.out_score64,
         a.flags, a.inexact);
     return cudaGetLastError();
 }
@@ -163,7 +164,7 @@ exact_scores_kernel(const __nv_bfloat16* __restrict__ qb, const __nv_bfloat16* _
 
 __global__ void __launch_bounds__(1024)
 exact_select_kernel(const double* __restrict__ scratch, int64_t nslots, int64_t capacity, int64_t head,
-                    int64_t base_seq, const int32_t* __restrict__ qids, int k,
+                    int64_t base_seq, int64_t seq_mul, int64_t seq_add, const int32_t* __restrict__ qids, int k,
                     int64_t* __restrict__ out_idx, float* __restrict__ out_score,
                     double* __restrict__ out_score64) {
     __shared__ double s_sc[32];
@@ -207,7 +208,7 @@ exact_select_kernel(const double* __restrict__ scratch, int64_t nslots, int64_t 
             }
             if (lane == 0) {
                 const bool ok = ba != INT64_MAX;
-                out_idx[q * k + r] = ok ? base_seq + ba : -1;
+                out_idx[q * k + r] = ok ? (base_seq + ba) * seq_mul + seq_add : -1;
                 out_score[q * k + r] = ok ? (float)bs : -INFINITY;
                 if (out_score64) out_score64[q * k + r] = ok ? bs : -INFINITY;
                 // once nothing is found, nothing will be found again: park the cursor at the end
@@ -221,8 +222,8 @@ exact_select_kernel(const double* __restrict__ scratch, int64_t nslots, int64_t 
 
 cudaError_t launch_exact(const void* qb, const void* vec, int ld, const int32_t* prio,
                          const uint64_t* tagmask, const int64_t* expires, int64_t nslots,
-                         int64_t capacity, int64_t head, int64_t base_seq, const int32_t* qids,
-                         int64_t nsel, int k, int32_t min_prio, uint64_t req, int64_t now_us,
+                         int64_t capacity, int64_t head, int64_t base_seq, int64_t seq_mul, int64_t seq_add,
+                         const int32_t* qids, int64_t nsel, int k, int32_t min_prio, uint64_t req, int64_t now_us,
                          double* scratch, int64_t* out_idx, float* out_score, double* out_score64,
                          cudaStream_t st) {
     if (nsel <= 0) return cudaSuccess;
@@ -235,7 +236,7 @@ cudaError_t launch_exact(const void* qb, const void* vec, int ld, const int32_t*
         if (e != cudaSuccess) return e;
     }
     exact_select_kernel<<<(unsigned)nsel, 1024, 0, st>>>(scratch, nslots, capacity, head, base_seq,
-                                                         qids, k, out_idx, out_score, out_score64);
+                                                         seq_mul, seq_add, qids, k, out_idx, out_score, out_score64);
     return cudaGetLastError();
 }
 

@@ -48,6 +48,7 @@ struct FinishArgs {
     const void* qb; const void* vec; int ld;
     int64_t nq, capacity, head, base_seq;
     int k; double err;
+    int64_t seq_mul, seq_add;   // reported index = seq * seq_mul + seq_add
     int64_t* out_idx; float* out_score; double* out_score64;
     uint8_t* flags; int32_t* inexact;
 };
@@ -55,7 +56,8 @@ cudaError_t launch_finish(const FinishArgs& a, cudaStream_t st);
 
 cudaError_t launch_exact(const void* qb, const void* vec, int ld, const int32_t* prio,
                          const uint64_t* tagmask, const int64_t* expires, int64_t nslots,
-                         int64_t capacity, int64_t head, int64_t base_seq, const int32_t* qids,
+                         int64_t capacity, int64_t head, int64_t base_seq, int64_t seq_mul, int64_t seq_add,
+                         const int32_t* qids,
                          int64_t nsel, int k, int32_t min_prio, uint64_t req, int64_t now_us,
                          double* scratch, int64_t* out_idx, float* out_score, double* out_score64,
                          cudaStream_t st);

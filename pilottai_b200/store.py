@@ -68,6 +68,19 @@ class SemanticStore:
     def set_list_len(self, n: int) -> None:
         check(self._lib.pilott_mem_set_option(self._h, 3, int(n)))
 
+    def set_profile(self, on: bool) -> None:
+        check(self._lib.pilott_mem_set_option(self._h, 4, 1 if on else 0))
+
+    def profile_read(self):
+        """(summed scan-kernel milliseconds, number of scans) since the last read."""
+        ms, n = C.c_double(), C.c_int64()
+        check(self._lib.pilott_mem_profile_read(self._h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+    def set_sequence_map(self, stride: int, offset: int) -> None:
+        check(self._lib.pilott_mem_set_option(self._h, 5, int(stride)))
+        check(self._lib.pilott_mem_set_option(self._h, 6, int(offset)))
+
     def set_debug(self, flags: int) -> None:
         check(self._lib.pilott_mem_set_option(self._h, 2, int(flags)))
 

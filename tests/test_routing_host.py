@@ -1,0 +1,121 @@
+"""CPU checks of the routing host logic: the per-agent fp64 terms, vocabularies and task
+encoding in pilottai_b200/routing.py, combined by a straight-line numpy emulation of what
+pilott_route_score does on the device, must reproduce the reference fixtures bit for bit."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from pilottai_b200 import routing as R
+
+CASES = ["small", "mid", "wide", "overloaded", "kat"]
+
+
+def emulate_kernel(enc, caps, spec, attr_flags, s12, t4, viable, u, max_tags, mode):
+    """What route_kernel computes, in plain Python over numpy scalars (fp64, one add each)."""
+    nt, na = enc["type"].shape[0], caps.shape[0]
+    out_a, out_s = np.full(nt, -1, np.int32), np.full(nt, np.nan)
+    for t in range(nt):
+        best, best_a = 0.0, -1
+        has_req, has_type = bool(enc["flags"][t] & 1), bool(enc["flags"][t] & 2)
+        ty = int(enc["type"][t])
+        for a in range(na):
+            if not viable[a]:
+                continue
+            missing = bool(np.any(enc["req"][t] & ~caps[a]))
+            tagc = int(sum(bin(int(x)).count("1") for x in (enc["tags"][t] & spec[a])))
+            tbit = ty >= 0 and bool((int(spec[a][ty >> 6]) >> (ty & 63)) & 1)
+            zero = has_req and (not (attr_flags[a] & 2) or missing)
+            sel = 0 if zero else (2 if (has_type and tbit) else 1)
+            sc = float(s12[a][sel])
+            if mode == 0:
+                sc = (sc + float(u[1 if tbit else 0][tagc])) + float(t4[a])
+            if mode == 2 and not sc > 0.0:
+                continue
+            if best_a < 0 or sc > best:
+                best, best_a = sc, a
+        out_a[t] = best_a
+        if best_a >= 0:
+            out_s[t] = best
+    return out_a, out_s
+
+
+def host_route(agents, tasks, mode, **cfg):
+    vocab = R.Vocab(agents)
+    enc = R.encode_tasks(tasks, vocab)
+    caps = np.stack([vocab.caps_mask(a.get("caps")) for a in agents])
+    spec = np.stack([vocab.spec_mask(a.get("specializations")) for a in agents])
+    attr = np.array([(2 if a.get("caps") is not None else 0) for a in agents], np.uint8)
+    max_tags = 64 * vocab.words
+    u = np.zeros((2, max_tags + 1))
+    for c in range(max_tags + 1):
+        u[0, c], u[1, c] = (0.1 * c) * 0.2, 0.3 * 0.2
+    s12, t4, viable = [], [], []
+    cand = cfg.get("candidates")
+    for a in agents:
+        if mode == "router":
+            s, t, ok = R.router_terms(a, cfg["load_threshold"])
+        elif mode == "load_balancer":
+            s, t, ok = R.lb_terms(a, cfg["lb_metrics"][a["id"]], cfg["max_tasks_per_agent"], cfg["overload_threshold"])
+        else:
+            s, t, ok = R.delegator_terms(a)
+        if cand is not None and a["id"] not in cand:
+            ok = False
+        s12.append(s); t4.append(t); viable.append(ok)
+    return emulate_kernel(enc, caps, spec, attr, np.array(s12), np.array(t4), viable, u, max_tags, R.MODE[mode])
+
+
+def _load(golden_dir, name):
+    with open(os.path.join(golden_dir, f"routing_{name}.json")) as f:
+        return json.load(f)
+
+
+def _ids(agents, idx):
+    return [agents[i]["id"] if i >= 0 else None for i in idx]
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_router_host_terms_match_reference(golden_dir, name):
+    g = _load(golden_dir, name)
+    idx, sc = host_route(g["agents"], g["tasks"], "router", load_threshold=g["load_threshold"])
+    assert _ids(g["agents"], idx) == [r["agent"] for r in g["router"]]
+    for s, r in zip(sc, g["router"]):
+        if r["agent"] is not None:
+            assert float(s).hex() == r["score"]
+    if name != "kat":
+        assert [R.PRIORITY_NAMES[R.task_priority_host(t)] for t in g["tasks"]] == [r["priority"] for r in g["router"]]
+
+
+@pytest.mark.parametrize("name", CASES[:-1])
+def test_load_balancer_host_terms_match_reference(golden_dir, name):
+    g = _load(golden_dir, name)
+    lbg, cfg = g["load_balancer"], g["lb_config"]
+    metrics = {a["id"]: R.lb_metrics_of(a, lbg["system_cpu_percent"], lbg["system_mem_percent"]) for a in g["agents"]}
+    for a in g["agents"]:
+        assert float(R.lb_composite(metrics[a["id"]], cfg["max_tasks_per_agent"])).hex() == lbg["composite"][a["id"]]
+    # candidates keep their list order == table order here (fixture candidates are a subsequence)
+    idx, sc = host_route(g["agents"], g["tasks"], "load_balancer", lb_metrics=metrics, candidates=set(lbg["candidates"]),
+                         max_tasks_per_agent=cfg["max_tasks_per_agent"], overload_threshold=cfg["overload_threshold"])
+    assert _ids(g["agents"], idx) == [r["agent"] for r in lbg["results"]]
+    for s, r in zip(sc, lbg["results"]):
+        if r["agent"] is not None:
+            assert float(s).hex() == r["score"]
+
+
+@pytest.mark.parametrize("name", CASES[:-1])
+def test_delegator_host_terms_match_reference(golden_dir, name):
+    g = _load(golden_dir, name)
+    idx, sc = host_route(g["agents"], g["tasks"], "delegator")
+    assert _ids(g["agents"], idx) == [r["agent"] for r in g["delegator"]]
+    for s, r in zip(sc, g["delegator"]):
+        if r["agent"] is not None:
+            assert float(s).hex() == r["score"]
+
+
+def test_vocab_reserves_unknown_capability_bit():
+    agents = [{"caps": ["a", "b"], "specializations": ["x"]}, {"caps": None, "specializations": None}]
+    v = R.Vocab(agents)
+    assert v.cap == {"a": 1, "b": 2} and v.spec == {"x": 0} and v.words == 1
+    assert int(v.req_mask(["a", "zzz"])[0]) == 0b011          # unknown -> bit 0, which no agent owns
+    assert int(v.tag_mask(["x", "x", "nope"])[0]) == 1
