@@ -14,9 +14,10 @@
 //
 // Warp roles (384 threads): 0 = TMA producer, 1 = MMA issuer, 2 = TMEM allocator,
 // 3 = idle, 4..11 = epilogue in two sets of four warps (TMEM lane quarter = warp % 4).
-// Set s drains accumulator stage s, i.e. every other corpus tile, with its own candidate
-// buffers, so each set has two tile-times per tile and every SM sub-partition holds two
-// epilogue warps that cover each other's latencies.
+// Set s drains columns [128*s, 128*s+128) of EVERY accumulator tile with its own candidate
+// buffers: the tile's epilogue time halves (an accumulator stage is busy for MMA time +
+// epilogue time, so with two stages the epilogue of one tile must fit in one MMA time), and
+// every SM sub-partition holds two epilogue warps that cover each other's latencies.
 // Pipelines: smem full/empty ring (TMA <-> MMA), TMEM full/empty x2 (MMA <-> epilogue).
 #include "common.cuh"
 #include "internal.h"
@@ -63,7 +64,7 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t rank)
     asm volatile(
         "{\n\t.reg .b32 ra;\n\t"
         "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
-        "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}"
+        "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t}"
         ::"r"(bar), "r"(rank) : "memory");
 }
 __device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
@@ -239,11 +240,11 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
         }
         for (int i = 0; i < ACC_STAGES; ++i) {
             mbar_init(bar_tfull + 8 * i, 1);
-            mbar_init(bar_tempty + 8 * i, 4 * CG);     // one arrive per epilogue warp per CTA
+            mbar_init(bar_tempty + 8 * i, 4 * EPI_SETS * CG);   // one arrive per epilogue warp per CTA
         }
         for (int i = 0; i < SC_RING; ++i) {
             mbar_init(bar_scfull + 8 * i, 1);
-            mbar_init(bar_scempty + 8 * i, 4);         // the four warps of the set that read the slot
+            mbar_init(bar_scempty + 8 * i, 4 * EPI_SETS);      // every epilogue warp reads part of the slot
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -316,7 +317,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
         __syncwarp();
     } else if (warp >= 4) {
         // ===== epilogue: scale, threshold, append, prune =====
-        const int set = (warp - 4) >> 2;                           // accumulator stage this set drains
+        const int set = (warp - 4) >> 2;                           // column half of every tile this set drains
         const int quarter = warp & 3;                              // TMEM lanes [32*quarter, +32)
         const int row = quarter * 32 + lane;                       // query row within the CTA tile
         uint64_t* rows = bufs + ((size_t)set * BM + quarter * 32) * CAPT;
@@ -328,7 +329,9 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
         const int64_t qrow = q0 + row;
         const bool has_q = qrow < nq;
         uint32_t aphase = 0;
-        for (int64_t t = t_lo + set; t < t_hi; t += EPI_SETS) {
+        int as = 0;
+        constexpr int CPS = BN / EPI_SETS;                         // columns per set
+        for (int64_t t = t_lo; t < t_hi; ++t) {
             const uint32_t n0 = (uint32_t)(t * BN);
             // Any list's KPT-th best score for this query bounds the global top-KPT from below, so
             // all CTAs sweeping the same query share one monotone threshold through gthr[query].
@@ -336,12 +339,12 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
             const int64_t ti = t - t_lo;
             const float* scb = ssc + (ti % SC_RING) * BN;
             mbar_wait(bar_scfull + 8 * (int)(ti % SC_RING), (uint32_t)((ti / SC_RING) & 1));
-            mbar_wait(bar_tfull + 8 * set, aphase);
+            mbar_wait(bar_tfull + 8 * as, aphase);
             tc_fence_after();
             if (g > f2ord(thr)) thr = ord2f(g);
-            const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + set * BN;
+            const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
 #pragma unroll 1
-            for (int c = 0; c < ((dbg & 1) ? 0 : BN); c += 16) {
+            for (int c = set * CPS; c < ((dbg & 1) ? 0 : (set + 1) * CPS); c += 16) {
                 uint32_t v[16];
                 tmem_ld16_issue(taddr0 + c, v);
                 float sc[16];
@@ -380,11 +383,11 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
             tc_fence_before();
             __syncwarp();
             if (lane == 0) {
-                if (CG == 2) mbar_arrive_cluster(bar_tempty + 8 * set, 0);
-                else mbar_arrive(bar_tempty + 8 * set);
+                if (CG == 2) mbar_arrive_cluster(bar_tempty + 8 * as, 0);
+                else mbar_arrive(bar_tempty + 8 * as);
                 mbar_arrive(bar_scempty + 8 * (int)(ti % SC_RING));     // scale slot may be refilled
             }
-            aphase ^= 1;
+            if (++as == ACC_STAGES) { as = 0; aphase ^= 1; }
         }
         // flush: final prune of every row, write this (slot, set) candidate list
         __syncwarp();
