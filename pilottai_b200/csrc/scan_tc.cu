@@ -72,21 +72,21 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
     return r;
 }
+// try_wait suspends the thread in hardware until the phase completes or the hint (ns) expires,
+// so a waiting role does not burn issue slots of the sub-partition it shares with epilogue warps.
 __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
     uint32_t ok;
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
         "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+        : "=r"(ok) : "r"(bar), "r"(parity), "r"(0x4000u) : "memory");
     return ok != 0;
 }
 // Bounded wait: a protocol bug traps (launch failure) instead of hanging the GPU.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    if (mbar_try_wait(bar, parity)) return;
-    const long long t0 = clock64();
-    for (uint32_t spins = 1; !mbar_try_wait(bar, parity); ++spins) {
-        if ((spins & 0xFFFu) == 0 && clock64() - t0 > 4000000000ll) __trap();
+    for (uint32_t spins = 0; !mbar_try_wait(bar, parity); ++spins) {
+        if (spins > (1u << 24)) __trap();
     }
 }
 
@@ -323,7 +323,6 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
         uint64_t* rows = bufs + ((size_t)set * BM + quarter * 32) * CAPT;
         uint64_t* mine = bufs + ((size_t)set * BM + row) * CAPT;
         const uint32_t head32 = (uint32_t)head, cap32 = (uint32_t)capacity;
-        constexpr int GRP = KPT == 16 ? 16 : 8;                    // elements per threshold test / fullness check
         float thr = -INFINITY;
         int cnt = 0, conv = 0;
         const int64_t qrow = q0 + row;
@@ -355,27 +354,40 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                 }
                 tmem_ld_wait();
                 if (dbg & 2) { if (v[0] == 0x7fc12345u && v[15] == 0x7fc54321u) thr = 1.f; continue; }
+                // Test groups of 4: one FMNMX tree + compare + vote per group.  fmaxf drops NaN
+                // (filtered rows), so a fully filtered group compares NaN >= thr == false.
+                bool touched = false;
 #pragma unroll
-                for (int g0 = 0; g0 < 16; g0 += GRP) {
-                    float s[GRP];
-                    bool hit = false;
+                for (int g0 = 0; g0 < 16; g0 += 4) {
+                    const float s0 = __uint_as_float(v[g0]) * sc[g0];
+                    const float s1 = __uint_as_float(v[g0 + 1]) * sc[g0 + 1];
+                    const float s2 = __uint_as_float(v[g0 + 2]) * sc[g0 + 2];
+                    const float s3 = __uint_as_float(v[g0 + 3]) * sc[g0 + 3];
+                    const float mx = fmaxf(fmaxf(s0, s1), fmaxf(s2, s3));
+                    if (__any_sync(FULL, mx >= thr)) {
+                        // slow path (warp-uniform entry): append the survivors of this group
+                        touched = true;
+                        const float s4[4] = {s0, s1, s2, s3};
 #pragma unroll
-                    for (int j = 0; j < GRP; ++j) {
-                        s[j] = __uint_as_float(v[g0 + j]) * sc[g0 + j];
-                        hit |= (s[j] >= thr);
-                    }
-                    if (__any_sync(FULL, hit)) {
-                        // slow path (warp-uniform entry): append survivors, prune full rows
-#pragma unroll
-                        for (int j = 0; j < GRP; ++j) {
-                            if (s[j] >= thr)
-                                mine[cnt++] = ((uint64_t)f2ord(s[j]) << 32) | (n0 + c + g0 + j);
+                        for (int j = 0; j < 4; ++j) {
+                            if (s4[j] >= thr)
+                                mine[cnt++] = ((uint64_t)f2ord(s4[j]) << 32) | (n0 + c + g0 + j);
                         }
-                        const unsigned full = __ballot_sync(FULL, cnt > CAPT - GRP);
+                    }
+                    if (KPT == 32 && (g0 & 4) && touched) {    // 32-entry lists: fullness check every 8
+                        touched = false;
+                        const unsigned full = __ballot_sync(FULL, cnt > CAPT - 8);
                         if (full) {
                             warp_prune_rows<CAPT, KPT>(full, rows, lane, cnt, conv, thr, head32, cap32);
                             if (((full >> lane) & 1u) && has_q) atomicMax(gthr + qrow, f2ord(thr));
                         }
+                    }
+                }
+                if (KPT == 16 && touched) {                    // 16-entry lists: once per 16 columns
+                    const unsigned full = __ballot_sync(FULL, cnt > CAPT - 16);
+                    if (full) {
+                        warp_prune_rows<CAPT, KPT>(full, rows, lane, cnt, conv, thr, head32, cap32);
+                        if (((full >> lane) & 1u) && has_q) atomicMax(gthr + qrow, f2ord(thr));
                     }
                 }
             }
