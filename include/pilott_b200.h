@@ -113,6 +113,35 @@ int pilott_mem_search_exact(pilott_mem_t* h, const float* q_dev, int64_t nq, con
                             int64_t now_us, int64_t* out_idx_dev, float* out_score_dev,
                             double* out_score64_dev, void* stream);
 
+/* Same search as pilott_mem_search_exact, same arguments and bit-identical results, but the
+ * call allocates nothing.  It has no counterpart in the reference.
+ *
+ * Who needs it: code that must not (or cannot) reach the CUDA allocator while it runs --
+ * PilottAI's single asyncio loop thread, where the device-wide synchronisation inside
+ * cudaMalloc/cudaFree would stall every other stream and coroutine; and processes in which a
+ * framework's caching allocator (PyTorch's, typically) already owns nearly all of HBM, so a
+ * raw cudaMalloc from this library fails although the store itself is resident.
+ * pilott_mem_search_exact grows per-handle scratch with cudaMalloc on demand; this variant
+ * keeps its scratch (converted queries + one fp64 score per selected query per stored row) in
+ * a fixed PILOTT_NOALLOC_SCRATCH_BYTES array inside the library's device image, which every
+ * GPU that loads the library holds until the process exits.  It calls no cudaMalloc, cudaFree
+ * or other allocating routine.
+ *
+ * Limit: round_up(nq * row_stride * 2, 256) + nsel * rows_held * 8 <= PILOTT_NOALLOC_SCRATCH_BYTES
+ * (e.g. 20 selected queries against 100 000 rows), and nsel <= 65535; beyond that the call
+ * fails with PILOTT_EINVAL and a message that states both numbers.
+ * First call on each device looks up the array's device address (cudaGetSymbolAddress) and
+ * caches it; make that first call before starting any stream capture.
+ * The array is shared by every call on the device and keeps the previous call's contents.
+ * Nothing in it needs to start at zero (each call rewrites what it reads), but two calls that
+ * overlap on the GPU -- different streams or different handles on one device -- race on it:
+ * serialise them. */
+#define PILOTT_NOALLOC_SCRATCH_BYTES (16u << 20)
+int pilott_mem_search_exact_noalloc(pilott_mem_t* h, const float* q_dev, int64_t nq,
+                                    const int32_t* query_ids_dev, int64_t nsel, int k, int32_t min_prio,
+                                    uint64_t req_tagmask, int64_t now_us, int64_t* out_idx_dev,
+                                    float* out_score_dev, double* out_score64_dev, void* stream);
+
 /* Replaces EnhancedMemory.cleanup's semantic-store pass (enhanced_memory.py:258-272):
  * drops expired rows and rebuilds the ring densely in insertion order.  `total` is
  * unchanged; the i-th oldest survivor is renumbered total - kept + i (the reference

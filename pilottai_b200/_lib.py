@@ -14,6 +14,7 @@ LIB_PATH = os.path.join(_HERE, "libpilott_b200.so")
 OK, EINVAL, ECUDA, ENOMEM, EUNSUPPORTED = 0, -1, -2, -3, -4
 MAX_FUSED_K = 32
 MAX_TAGS = 64
+NOALLOC_SCRATCH_BYTES = 16 << 20
 
 c_i64, c_i32, c_u64, c_vp = C.c_int64, C.c_int32, C.c_uint64, C.c_void_p
 
@@ -38,6 +39,8 @@ SIGNATURES = {
                                          c_vp, C.POINTER(c_i32)]),
     "pilott_mem_search_exact": (C.c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, C.c_int, c_i32, c_u64, c_i64,
                                           c_vp, c_vp, c_vp, c_vp]),
+    "pilott_mem_search_exact_noalloc": (C.c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, C.c_int, c_i32, c_u64, c_i64,
+                                                  c_vp, c_vp, c_vp, c_vp]),
     "pilott_mem_compact": (C.c_int, [c_vp, c_i64, C.POINTER(c_i64), c_vp]),
     "pilott_mem_export": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "pilott_topk_merge": (C.c_int, [c_vp, c_vp, C.c_int, c_i64, C.c_int, c_vp, c_vp, c_vp, c_vp]),

@@ -6,6 +6,7 @@
 
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
 #include <vector>
@@ -103,6 +104,13 @@ struct DeviceGuard {
 };
 
 }  // namespace
+
+// Scratch for pilott_mem_search_exact_noalloc: lives in the library's own device image, so it
+// exists on every GPU that loads the library from load time until the process exits and no
+// call ever has to allocate it.  In host code this name is only a handle the runtime
+// understands -- it is NOT a device address and must never be handed to a kernel; the real
+// address is looked up per device by noalloc_scratch() below.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[PILOTT_NOALLOC_SCRATCH_BYTES];
 
 struct pilott_mem {
     int dim = 0, ld = 0, device = 0, num_sms = 0;
@@ -669,6 +677,63 @@ int pilott_task_priority(const uint8_t* urgent_dev, const int32_t* complexity_de
     if (nt == 0) return PILOTT_OK;
     if (!urgent_dev || !complexity_dev || !n_deps_dev || !out_dev) return fail(PILOTT_EINVAL, "NULL pointer");
     CK(pilott::launch_task_priority(urgent_dev, complexity_dev, n_deps_dev, nt, out_dev, (cudaStream_t)stream));
+    return PILOTT_OK;
+}
+
+// Device address of g_noalloc_scratch on `device` (which must be the current device).  The
+// lookup runs once per device; later calls return the cached pointer.
+namespace {
+constexpr int kNoallocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+void* g_noalloc_ptr[kNoallocMaxDevices] = {};
+
+int noalloc_scratch(int device, unsigned char** out) {
+    if (device < 0 || device >= kNoallocMaxDevices) return fail(PILOTT_EINVAL, "device index out of range");
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[device]) {
+        void* ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch);
+        if (e != cudaSuccess) return fail_cuda(e, "cudaGetSymbolAddress(g_noalloc_scratch)");
+        g_noalloc_ptr[device] = ptr;
+    }
+    *out = static_cast<unsigned char*>(g_noalloc_ptr[device]);
+    return PILOTT_OK;
+}
+}  // namespace
+
+int pilott_mem_search_exact_noalloc(pilott_mem_t* h, const float* q_dev, int64_t nq,
+                                    const int32_t* query_ids_dev, int64_t nsel, int k, int32_t min_prio,
+                                    uint64_t req_tagmask, int64_t now_us, int64_t* out_idx_dev,
+                                    float* out_score_dev, double* out_score64_dev, void* stream) {
+    if (!h) return fail(PILOTT_EINVAL, "handle is NULL");
+    if (nq < 0) return fail(PILOTT_EINVAL, "nq is negative");
+    if (k < 1) return fail(PILOTT_EINVAL, "k must be >= 1");
+    if (!query_ids_dev) nsel = nq;
+    if (nq == 0 || nsel <= 0) return PILOTT_OK;
+    if (!q_dev || !out_idx_dev || !out_score_dev) return fail(PILOTT_EINVAL, "NULL query or output pointer");
+    if (nsel > 65535) return fail(PILOTT_EINVAL, "pilott_mem_search_exact_noalloc: at most 65535 selected queries per call");
+    // Layout inside the fixed buffer: [bf16 queries, nq x row_stride][fp64 scores, nsel x rows held]
+    const uint64_t q_bytes = (uint64_t)round_up(nq * (int64_t)h->ld * 2, 256);
+    const uint64_t s_bytes = (uint64_t)nsel * (uint64_t)(h->count > 0 ? h->count : 1) * 8u;
+    if (q_bytes + s_bytes > (uint64_t)PILOTT_NOALLOC_SCRATCH_BYTES)
+        return fail(PILOTT_EINVAL,
+                    "pilott_mem_search_exact_noalloc: this call needs " + std::to_string(q_bytes + s_bytes) +
+                    " bytes of scratch but the built-in buffer holds " + std::to_string(PILOTT_NOALLOC_SCRATCH_BYTES) +
+                    " (8 bytes per selected query per stored row): select fewer queries per call, or use "
+                    "pilott_mem_search_exact, which allocates");
+    DeviceGuard g(h->device);
+    unsigned char* scratch = nullptr;
+    int rc = noalloc_scratch(h->device, &scratch);      // first call on this device: symbol lookup
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    // Nothing in the buffer has to start at zero: the query block and every score the selection
+    // reads are rewritten by the two kernels below before they are read.
+    CK(pilott::launch_convert_queries(q_dev, nq, h->dim, h->ld, scratch, st));
+    CK(pilott::launch_exact(scratch, h->vec, h->ld, h->prio, h->tagmask, h->expires, h->count, h->capacity,
+                            h->head, h->total - h->count, h->seq_mul, h->seq_add, query_ids_dev, nsel, k,
+                            min_prio, req_tagmask, now_us, reinterpret_cast<double*>(scratch + q_bytes),
+                            out_idx_dev, out_score_dev, out_score64_dev, st));
+    h->launches += 3;
     return PILOTT_OK;
 }
 

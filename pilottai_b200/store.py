@@ -201,6 +201,24 @@ class SemanticStore:
                                                 self._stream()))
         return idx, sc, sc64
 
+    def search_exact_noalloc(self, q, k: int, out, query_ids=None, min_priority: int = 0,
+                             req_tagmask: int = 0, now_us: int = 0):
+        """Exact fp64 search that allocates nothing: for callers that cannot touch the CUDA
+        allocator while they run (the asyncio loop thread, where cudaMalloc's device-wide
+        sync would stall everything else; processes whose framework allocator already owns
+        HBM).  Same results as search_exact.  The caller passes every buffer: q (CUDA fp32
+        [nq, dim], contiguous), out = (idx int64, score fp32, score64 fp64) CUDA tensors
+        [nq, k], query_ids an int32 CUDA tensor or None.  Scratch is the library's fixed
+        16 MiB device array, so nq * row_stride * 2 + n_selected * rows_held * 8 bytes must
+        fit in it (PilottError otherwise); calls that overlap on the GPU share that array and
+        race.  The first call on a device should precede any stream capture."""
+        idx, sc, sc64 = out
+        nsel = q.shape[0] if query_ids is None else query_ids.numel()
+        check(self._lib.pilott_mem_search_exact_noalloc(
+            self._h, ptr(q), q.shape[0], ptr(query_ids), nsel, int(k), int(min_priority), int(req_tagmask),
+            int(now_us), ptr(idx), ptr(sc), ptr(sc64), self._stream()))
+        return idx, sc, sc64
+
     # -- maintenance ----------------------------------------------------------------------
     def compact(self, now_us: int) -> Tuple[int, np.ndarray]:
         n = self.count
