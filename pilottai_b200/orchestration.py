@@ -1,0 +1,443 @@
+"""Drop-ins for the reference's routing / balancing / delegation classes, scored on the GPU.
+
+Same class names, constructor arguments, coroutine names, config fields/ranges and error
+behaviour as
+  pilott/core/router.py                     TaskRouter, RouterConfig, TaskPriority
+  pilott/orchestration/load_balancer.py     LoadBalancer, LoadBalancerConfig, LoadMetrics
+  pilott/delegation/task_delegator.py       TaskDelegator
+written from scratch around `RoutingEngine` (pilottai_b200/routing.py).  Each scoring pass
+takes ONE metrics snapshot per agent and scores every task of the batch against it in one
+kernel call; the reference never mutates agent load inside a pass either.
+Not reproduced on purpose: the task-independent 5 s score cache (router.py:70-77) and the
+blocking `psutil.cpu_percent(interval=1)` per agent (load_balancer.py:101).
+"""
+from __future__ import annotations
+
+import asyncio
+import logging
+import weakref
+from collections import defaultdict
+from datetime import datetime, timedelta
+from enum import Enum
+from typing import Any, Dict, List, Optional, Sequence, Tuple
+
+import psutil
+from pydantic import BaseModel, Field
+
+from .routing import (PRIORITY_NAMES, RoutingEngine, features_from_agent, lb_composite,
+                      task_priority_host)
+
+
+class TaskPriority(str, Enum):
+    LOW = "low"
+    MEDIUM = "medium"
+    HIGH = "high"
+    CRITICAL = "critical"
+
+
+class RouterConfig(BaseModel):                                     # router.py:15-20
+    load_check_interval: int = Field(ge=1, default=5)
+    max_queue_size: int = Field(gt=0, default=100)
+    routing_timeout: int = Field(gt=0, default=30)
+    max_retry_attempts: int = Field(ge=0, default=3)
+    load_threshold: float = Field(ge=0.0, le=1.0, default=0.8)
+
+
+def _agent_list(container) -> List[Any]:
+    """`Serve.agents` is a dict role -> agent (pilott.py:93); the reference router iterates it
+    as if it were a list (router.py:67).  Accept both."""
+    if container is None:
+        return []
+    if isinstance(container, dict):
+        return list(container.values())
+    if hasattr(container, "values") and not isinstance(container, (list, tuple)):
+        return list(container.values())
+    return list(container)
+
+
+class _EngineCache:
+    """Keeps a RoutingEngine per agent population; metrics are re-snapshotted every pass."""
+
+    def __init__(self, device: int):
+        self.device, self._eng = device, None
+
+    async def snapshot(self, agents: Sequence[Any], extra=None) -> Tuple[RoutingEngine, List[dict]]:
+        rows = [await features_from_agent(a) for a in agents]
+        if extra:
+            for r in rows:
+                r.update(extra.get(r["id"], {}))
+        self._eng = RoutingEngine(rows, self.device)       # tables are small (KBs); rebuilt per pass
+        return self._eng, rows
+
+
+class TaskRouter:
+    def __init__(self, pilott: Any, config: Optional[Dict] = None, *, device: int = 0):
+        self.pilott = pilott
+        self.config = RouterConfig(**(config or {}))
+        self._router_lock = asyncio.Lock()
+        self._cache = _EngineCache(device)
+        self.logger = logging.getLogger("TaskRouter")
+
+    async def _attempt_batch(self, tasks: Sequence[Dict]) -> List[Optional[str]]:
+        agents = _agent_list(getattr(self.pilott, "agents", None))
+        if not agents or not tasks:
+            return [None] * len(tasks)
+        eng, rows = await self._cache.snapshot(agents)
+        idx, _ = await asyncio.to_thread(eng.route, list(tasks), "router", load_threshold=self.config.load_threshold)
+        return [rows[i]["id"] if i >= 0 else None for i in idx]
+
+    async def route_tasks_batch(self, tasks: Sequence[Dict]) -> List[Optional[str]]:
+        """One snapshot, one kernel call: agent id (or None) per task.  No retries."""
+        async with self._router_lock:
+            return await self._attempt_batch(tasks)
+
+    async def route_task(self, task: Dict) -> Optional[str]:      # router.py:34-49
+        try:
+            async with asyncio.timeout(self.config.routing_timeout):
+                async with self._router_lock:
+                    for _ in range(self.config.max_retry_attempts):
+                        agent_id = (await self._attempt_batch([task]))[0]
+                        if agent_id:
+                            return agent_id
+                        await asyncio.sleep(1)
+                    return None
+        except asyncio.TimeoutError:
+            self.logger.error("Task routing timed out")
+            raise RuntimeError("Task routing timed out")
+        except Exception as e:
+            self.logger.error(f"Routing error: {str(e)}")
+            raise
+
+    def get_task_priority(self, task: Dict) -> TaskPriority:       # router.py:135-145
+        return TaskPriority(PRIORITY_NAMES[task_priority_host(task)])
+
+
+# ------------------------------------------------------------------------------------------------
+class LoadMetrics(BaseModel):                                      # load_balancer.py:13-20
+    cpu_usage: float = 0.0
+    memory_usage: float = 0.0
+    queue_size: int = 0
+    active_tasks: int = 0
+    total_tasks: int = 0
+    error_rate: float = 0.0
+    timestamp: datetime = Field(default_factory=datetime.now)
+
+
+class LoadBalancerConfig(BaseModel):                               # load_balancer.py:22-30
+    check_interval: int = Field(ge=1, default=30)
+    overload_threshold: float = Field(ge=0.0, le=1.0, default=0.8)
+    underload_threshold: float = Field(ge=0.0, le=1.0, default=0.2)
+    max_tasks_per_agent: int = Field(ge=1, default=10)
+    balance_batch_size: int = Field(ge=1, default=3)
+    min_load_difference: float = Field(ge=0.0, le=1.0, default=0.3)
+    metrics_retention_period: int = Field(ge=0, default=3600)
+    task_move_timeout: int = Field(ge=1, default=30)
+
+
+def _lm_dict(m: LoadMetrics) -> dict:
+    return {"cpu_usage": m.cpu_usage, "memory_usage": m.memory_usage, "queue_size": m.queue_size,
+            "active_tasks": m.active_tasks, "total_tasks": m.total_tasks, "error_rate": m.error_rate}
+
+
+class LoadBalancer:
+    def __init__(self, orchestrator, config: Optional[Dict] = None, *, device: int = 0):
+        try:
+            self.orchestrator = weakref.proxy(orchestrator)
+        except TypeError:
+            self.orchestrator = orchestrator
+        self.config = LoadBalancerConfig(**(config or {}))
+        self.logger = logging.getLogger("LoadBalancer")
+        self.running = False
+        self.balancing_task: Optional[asyncio.Task] = None
+        self._balance_lock = asyncio.Lock()
+        self._metrics_history: Dict[str, List[LoadMetrics]] = {}
+        self._last_balance_time = datetime.now()
+        self._safe_mode = True
+        self._cache = _EngineCache(device)
+
+    async def start(self):
+        if self.running:
+            return
+        self.running = True
+        self.balancing_task = asyncio.create_task(self._balancing_loop())
+
+    async def stop(self):
+        if not self.running:
+            return
+        self.running = False
+        if self.balancing_task:
+            self.balancing_task.cancel()
+            try:
+                await self.balancing_task
+            except asyncio.CancelledError:
+                pass
+
+    async def _balancing_loop(self):
+        while self.running:
+            try:
+                async with self._balance_lock:
+                    await self._balance_system_load()
+                await asyncio.sleep(self.config.check_interval)
+            except asyncio.CancelledError:
+                break
+            except Exception as e:
+                self.logger.error(f"Error in balancing loop: {str(e)}")
+                await asyncio.sleep(self.config.check_interval)
+
+    def _children(self) -> Dict[str, Any]:
+        kids = getattr(self.orchestrator, "child_agents", {})
+        return dict(kids.items()) if hasattr(kids, "items") else {a.id: a for a in kids}
+
+    async def _get_available_agents(self) -> List[Any]:
+        return [a for a in self._children().values() if getattr(a.status, "value", a.status) != "stopped"]
+
+    async def _balance_system_load(self):                          # load_balancer.py:85-94
+        try:
+            current = await self._collect_system_metrics()
+            self._update_metrics_history(current)
+            over, under = await self._analyze_agent_loads(current)
+            if not over or not under:
+                return
+            await self._redistribute_tasks(over, under, current)
+        except Exception as e:
+            self.logger.error(f"Load balancing error: {str(e)}")
+
+    async def _collect_system_metrics(self) -> Dict[str, LoadMetrics]:     # :96-119, one psutil sample per pass
+        sys_cpu = psutil.cpu_percent(interval=None) / 100.0
+        sys_mem = psutil.virtual_memory().percent / 100.0
+        out: Dict[str, LoadMetrics] = {}
+        for agent in await self._get_available_agents():
+            try:
+                m = await agent.get_metrics()
+                out[agent.id] = LoadMetrics(
+                    cpu_usage=max(sys_cpu, m.get("cpu_usage", 0.0)), memory_usage=max(sys_mem, m.get("memory_usage", 0.0)),
+                    queue_size=m.get("queue_size", 0), active_tasks=m.get("active_tasks", 0),
+                    total_tasks=m.get("total_tasks", 0), error_rate=1 - m.get("success_rate", 0.0))
+                lm = out[agent.id]
+                if lm.cpu_usage > self.config.overload_threshold or lm.memory_usage > self.config.overload_threshold:
+                    await self._handle_overload(agent.id)
+            except Exception as e:
+                self.logger.error(f"Error collecting metrics for agent {agent.id}: {str(e)}")
+        return out
+
+    async def _handle_overload(self, agent_id: str):
+        try:
+            await self._children()[agent_id].pause_task_acceptance()
+        except Exception as e:
+            self.logger.error(f"Error handling overload for agent {agent_id}: {str(e)}")
+
+    def _update_metrics_history(self, metrics: Dict[str, LoadMetrics]):    # :129-141
+        keep_after = datetime.now() - timedelta(seconds=self.config.metrics_retention_period)
+        for aid, m in metrics.items():
+            hist = self._metrics_history.setdefault(aid, [])
+            hist.append(m)
+            self._metrics_history[aid] = [x for x in hist if x.timestamp > keep_after]
+
+    def _calculate_composite_load(self, metrics: LoadMetrics) -> float:    # :172-178
+        return lb_composite(_lm_dict(metrics), self.config.max_tasks_per_agent)
+
+    def _calculate_load_trend(self, agent_id: str) -> float:               # :161-170
+        hist = self._metrics_history.get(agent_id, [])[-5:]
+        if len(hist) < 2:
+            return 0.0
+        loads = [self._calculate_composite_load(m) for m in hist]
+        return (loads[-1] - loads[0]) / len(loads)
+
+    async def _analyze_agent_loads(self, current: Dict[str, LoadMetrics]) -> Tuple[List[str], List[str]]:   # :143-159
+        over, under = [], []
+        for aid, m in current.items():
+            trend, load = self._calculate_load_trend(aid), self._calculate_composite_load(m)
+            if load > self.config.overload_threshold and trend > 0:
+                over.append(aid)
+            elif load < self.config.underload_threshold and trend < 0:
+                under.append(aid)
+        return over, under
+
+    async def _find_best_agents(self, tasks: Sequence[Dict], candidates: List[str],
+                                current_metrics: Dict[str, LoadMetrics]) -> List[Optional[str]]:
+        """Batched `_find_best_agent`: every task against the candidate list, one kernel call."""
+        kids = self._children()
+        cands = [c for c in candidates if c in kids and c in current_metrics]
+        if not cands or not tasks:
+            return [None] * len(tasks)
+        eng, rows = await self._cache.snapshot([kids[c] for c in cands])
+        lbm = {c: _lm_dict(current_metrics[c]) for c in cands}
+        idx, _ = await asyncio.to_thread(
+            eng.route, list(tasks), "load_balancer", lb_metrics=lbm,
+            max_tasks_per_agent=self.config.max_tasks_per_agent, overload_threshold=self.config.overload_threshold)
+        return [rows[i]["id"] if i >= 0 else None for i in idx]
+
+    async def _find_best_agent(self, task: Dict, candidates: List[str],
+                               current_metrics: Dict[str, LoadMetrics]) -> Optional[str]:         # :268-292
+        return (await self._find_best_agents([task], candidates, current_metrics))[0]
+
+    def _is_task_moveable(self, task) -> bool:                              # :260-266
+        get = task.get if hasattr(task, "get") else (lambda k, d=None: getattr(task, k, d))
+        return get("status") == "pending" and not get("locked", False) and not get("unmoveable", False)
+
+    async def _get_moveable_tasks(self, agent_id: str) -> List[Dict]:
+        try:
+            return [t for t in self._children()[agent_id].tasks.values() if self._is_task_moveable(t)]
+        except Exception as e:
+            self.logger.error(f"Error getting moveable tasks: {str(e)}")
+            return []
+
+    async def _redistribute_tasks(self, overloaded: List[str], underloaded: List[str],
+                                  current_metrics: Dict[str, LoadMetrics]):                     # :180-218
+        for over_id in overloaded:
+            try:
+                tasks = await self._get_moveable_tasks(over_id)
+                tasks.sort(key=lambda x: x.get("priority", 0), reverse=True)
+                tasks = tasks[: self.config.balance_batch_size * 4]
+                targets = await self._find_best_agents(tasks, underloaded, current_metrics)
+                moves = 0
+                for task, best in zip(tasks, targets):
+                    if moves >= self.config.balance_batch_size:
+                        break
+                    if not best:
+                        continue
+                    try:
+                        async with asyncio.timeout(self.config.task_move_timeout):
+                            await self._move_task(task, over_id, best)
+                            moves += 1
+                    except asyncio.TimeoutError:
+                        self.logger.error(f"Task move timed out for task {task['id']}")
+                    except Exception as e:
+                        self.logger.error(f"Failed to move task {task['id']}: {str(e)}")
+                if moves > 0:
+                    self._last_balance_time = datetime.now()
+            except Exception as e:
+                self.logger.error(f"Error redistributing tasks for agent {over_id}: {str(e)}")
+
+    async def _move_task(self, task: Dict, from_agent_id: str, to_agent_id: str):                # :220-251
+        kids = self._children()
+        src, dst = kids[from_agent_id], kids[to_agent_id]
+        task["locked"] = True
+        backup = task.copy() if self._safe_mode else None
+        try:
+            await src.remove_task(task["id"])
+            await dst.add_task(task)
+            task["moved_at"] = datetime.now().isoformat()
+            task["moved_from"], task["moved_to"] = from_agent_id, to_agent_id
+        except Exception as e:
+            self.logger.error(f"Task movement failed: {str(e)}")
+            if backup is not None:
+                try:
+                    await src.add_task(backup)
+                except Exception as restore_error:
+                    self.logger.error(f"Failed to restore task {task['id']}: {str(restore_error)}")
+            raise
+        finally:
+            task["locked"] = False
+
+    async def get_metrics(self) -> Dict[str, Any]:
+        current = await self._collect_system_metrics()
+        loads = {a: self._calculate_composite_load(m) for a, m in current.items()}
+        return {"active_agents": len(await self._get_available_agents()),
+                "overloaded_agents": sum(1 for v in loads.values() if v > self.config.overload_threshold),
+                "underloaded_agents": sum(1 for v in loads.values() if v < self.config.underload_threshold),
+                "last_balance_time": self._last_balance_time.isoformat(),
+                "metrics_history": {a: [m.model_dump() for m in h] for a, h in self._metrics_history.items()}}
+
+
+# ------------------------------------------------------------------------------------------------
+class DelegationMetrics(BaseModel):                                 # task_delegator.py:8-15
+    success_count: int = 0
+    failure_count: int = 0
+    total_execution_time: float = 0
+    avg_execution_time: float = 0
+    last_success: Optional[datetime] = None
+    last_failure: Optional[datetime] = None
+    error_types: Dict[str, int] = Field(default_factory=dict)
+
+
+class TaskDelegator:
+    def __init__(self, agent, *, device: int = 0):
+        self.agent = agent
+        self.delegation_history: Dict[str, List[Dict]] = defaultdict(list)
+        self.agent_metrics: Dict[str, DelegationMetrics] = {}
+        self.active_delegations: Dict[str, Dict] = {}
+        self.logger = logging.getLogger(f"TaskDelegator_{getattr(agent, 'id', 'agent')}")
+        self._delegation_lock = asyncio.Lock()
+        self.MAX_HISTORY_PER_AGENT = 1000
+        self._cache = _EngineCache(device)
+
+    async def _should_delegate(self, task: Dict) -> bool:           # task_delegator.py:328-349
+        try:
+            cfg = self.agent.config
+            if not cfg.allow_delegation:
+                return False
+            if (await self.agent.get_metrics())["queue_utilization"] > 0.8:
+                return True
+            if task.get("complexity", 1) > cfg.max_task_complexity:
+                return True
+            if task.get("required_capabilities"):
+                if set(task["required_capabilities"]) - set(cfg.required_capabilities):
+                    return True
+            return False
+        except Exception as e:
+            self.logger.error(f"Error checking delegation: {str(e)}")
+            return False
+
+    async def _find_best_agents(self, tasks: Sequence[Dict]) -> List[Optional[Any]]:
+        kids = dict(self.agent.child_agents.items())
+        if not kids or not tasks:
+            return [None] * len(tasks)
+        counts = defaultdict(int)
+        for d in self.active_delegations.values():
+            counts[d["agent_id"]] += 1
+        agents = list(kids.values())
+        extra = {a.id: {"active_delegations": counts[a.id]} for a in agents}
+        eng, rows = await self._cache.snapshot(agents, extra)
+        idx, _ = await asyncio.to_thread(eng.route, list(tasks), "delegator")
+        return [agents[i] if i >= 0 else None for i in idx]
+
+    async def _find_best_agent(self, task: Dict) -> Optional[Any]:  # :60-90
+        try:
+            async with asyncio.timeout(10):
+                return (await self._find_best_agents([task]))[0]
+        except asyncio.TimeoutError:
+            self.logger.error("Agent selection timed out")
+            return None
+        except Exception as e:
+            self.logger.error(f"Error finding best agent: {str(e)}")
+            return None
+
+    async def evaluate_delegation(self, task: Dict) -> Tuple[bool, Optional[str]]:   # :41-58
+        try:
+            async with self._delegation_lock:
+                if not await self._should_delegate(task):
+                    return False, None
+                best = await self._find_best_agent(task)
+                if best:
+                    self.active_delegations[task["id"]] = {"agent_id": best.id, "started_at": datetime.now(), "task": task}
+                    return True, best.id
+                return False, None
+        except Exception as e:
+            self.logger.error(f"Delegation evaluation failed: {str(e)}")
+            return False, None
+
+    def record_delegation(self, agent_id: str, task: Dict, result: Dict):            # :183-219 (condensed)
+        ok = result.get("status") == "completed"
+        hist = self.delegation_history[agent_id]
+        hist.append({"task_id": task["id"], "timestamp": datetime.now().isoformat(), "success": ok,
+                     "execution_time": result.get("execution_time"), "error": result.get("error")})
+        del hist[: max(0, len(hist) - self.MAX_HISTORY_PER_AGENT)]
+        m = self.agent_metrics.setdefault(agent_id, DelegationMetrics())
+        if ok:
+            m.success_count += 1
+            m.last_success = datetime.now()
+        else:
+            m.failure_count += 1
+            m.last_failure = datetime.now()
+            et = str(result.get("error_type", "unknown"))
+            m.error_types[et] = m.error_types.get(et, 0) + 1
+        t = result.get("execution_time") or 0
+        m.total_execution_time += t
+        m.avg_execution_time = m.total_execution_time / max(1, m.success_count + m.failure_count)
+        self.active_delegations.pop(task["id"], None)
+
+    async def get_metrics(self) -> Dict[str, Any]:
+        return {"active_delegations": len(self.active_delegations),
+                "agent_metrics": {a: m.model_dump() for a, m in self.agent_metrics.items()},
+                "history_size": sum(len(h) for h in self.delegation_history.values())}

@@ -25,22 +25,6 @@ def shard_rows(first_global: int, n: int, rank: int, world: int) -> np.ndarray:
     return np.arange(start, n, world, dtype=np.int64)
 
 
-def merge_gathered_cpu(idx: np.ndarray, score: np.ndarray, k: int):
-    """Host restatement of pilott_topk_merge for the gloo/CPU tests of the exchange step:
-    [shards, Q, k] -> [Q, k] by (score desc, index asc); -1 entries are padding."""
-    shards, nq, kk = idx.shape
-    flat_i = np.transpose(idx, (1, 0, 2)).reshape(nq, shards * kk)
-    flat_s = np.transpose(score, (1, 0, 2)).reshape(nq, shards * kk)
-    out_i = np.full((nq, k), -1, np.int64)
-    out_s = np.full((nq, k), -np.inf, np.float64)
-    for q in range(nq):
-        ok = flat_i[q] >= 0
-        ci, cs = flat_i[q][ok], flat_s[q][ok]
-        order = np.lexsort((ci, -cs))[:k]
-        out_i[q, : order.size], out_s[q, : order.size] = ci[order], cs[order]
-    return out_i, out_s
-
-
 class ShardedSemanticStore:
     def __init__(self, dim: int, capacity: int, rank: int, world: int, device: int,
                  group: Optional[dist.ProcessGroup] = None):

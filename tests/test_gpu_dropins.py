@@ -1,0 +1,168 @@
+"""GPU tests of the reference-facing drop-in classes (same names/signatures as the reference):
+EnhancedMemory, TaskRouter, LoadBalancer, TaskDelegator.  Routing results are compared with the
+fixtures produced by the unmodified reference; memory semantics with the rules the reference
+specifies (filters, expiry, ring capacity, error strings)."""
+import asyncio
+import json
+import os
+import types
+
+import numpy as np
+import pytest
+
+from oracle import routing_oracle as ro
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    torch = pytest.importorskip("torch")
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    return torch
+
+
+def _load(golden_dir, name):
+    with open(os.path.join(golden_dir, f"routing_{name}.json")) as f:
+        return json.load(f)
+
+
+class FakeAgent:
+    """Stands in for BaseAgent: the attributes and the get_metrics() the scorers read."""
+
+    def __init__(self, row):
+        self.row, self.id, self.status = row, row["id"], row["status"]
+        cfg = {"max_queue_size": row["max_queue_size"]}
+        if row["caps"] is not None:
+            cfg["required_capabilities"] = list(row["caps"])
+        self.config = types.SimpleNamespace(**cfg)
+        if row["specializations"] is not None:
+            self.specializations = list(row["specializations"])
+        if row["max_concurrent_tasks"] is not None:
+            self.max_concurrent_tasks = row["max_concurrent_tasks"]
+        self.tasks = {}
+
+    async def get_metrics(self):
+        return ro.agent_metrics(self.row)
+
+
+def test_task_router_dropin_matches_reference(torch_cuda, golden_dir, monkeypatch):
+    from pilottai_b200 import TaskRouter, TaskPriority
+    g = _load(golden_dir, "mid")
+    agents = [FakeAgent(r) for r in g["agents"]]
+    for container in (agents, {f"role{i}": a for i, a in enumerate(agents)}):       # list or Serve-style dict
+        router = TaskRouter(types.SimpleNamespace(agents=container), {"load_threshold": g["load_threshold"]})
+        got = asyncio.run(router.route_tasks_batch(g["tasks"]))
+        assert got == [r["agent"] for r in g["router"]]
+    assert asyncio.run(router.route_task(g["tasks"][0])) == g["router"][0]["agent"]
+    assert [router.get_task_priority(t).value for t in g["tasks"]] == [r["priority"] for r in g["router"]]
+    assert router.get_task_priority({"urgent": True}) is TaskPriority.CRITICAL
+    with pytest.raises(Exception):
+        TaskRouter(None, {"load_threshold": 1.5})                                      # RouterConfig range kept
+
+    # nobody viable -> None after max_retry_attempts attempts (sleep patched out)
+    g2 = _load(golden_dir, "overloaded")
+    slept = []
+
+    async def fake_sleep(s):
+        slept.append(s)
+    monkeypatch.setattr(asyncio, "sleep", fake_sleep)
+    r2 = TaskRouter(types.SimpleNamespace(agents=[FakeAgent(r) for r in g2["agents"]]))
+    assert asyncio.run(r2.route_task(g2["tasks"][0])) is None
+    assert slept == [1, 1, 1]
+
+
+def test_load_balancer_dropin_matches_reference(torch_cuda, golden_dir):
+    from pilottai_b200 import LoadBalancer, LoadBalancerConfig, LoadMetrics
+    g = _load(golden_dir, "mid")
+    lbg = g["load_balancer"]
+    kids = {r["id"]: FakeAgent(r) for r in g["agents"]}
+
+    class Orch:
+        child_agents = kids
+        verbose = False
+    orch = Orch()
+    lb = LoadBalancer(orch, g["lb_config"])
+    assert isinstance(lb.config, LoadBalancerConfig) and lb.config.balance_batch_size == 3
+    metrics = {r["id"]: LoadMetrics(**ro.lb_metrics(r, lbg["system_cpu_percent"], lbg["system_mem_percent"]))
+               for r in g["agents"]}
+    got = asyncio.run(lb._find_best_agents(g["tasks"], lbg["candidates"], metrics))
+    assert got == [r["agent"] for r in lbg["results"]]
+    assert asyncio.run(lb._find_best_agent(g["tasks"][3], lbg["candidates"], metrics)) == lbg["results"][3]["agent"]
+    for aid, want in lbg["composite"].items():
+        assert float(lb._calculate_composite_load(metrics[aid])).hex() == want
+    for aid, h in lbg["history"].items():
+        lb._metrics_history[aid] = [LoadMetrics(**m) for m in h]
+        assert float(lb._calculate_load_trend(aid)).hex() == lbg["trends"][aid]
+    current = {aid: lb._metrics_history[aid][-1] for aid in lbg["history"]}
+    over, under = asyncio.run(lb._analyze_agent_loads(current))
+    assert over == lbg["overloaded"] and under == lbg["underloaded"]
+
+    async def start_stop():
+        await lb.start(); await lb.stop()
+    asyncio.run(start_stop())
+    assert not lb.running                                  # what the reference's own test asserts
+
+
+def test_task_delegator_dropin_matches_reference(torch_cuda, golden_dir):
+    from pilottai_b200 import TaskDelegator
+    g = _load(golden_dir, "mid")
+    kids = {r["id"]: FakeAgent(r) for r in g["agents"]}
+    mgr = types.SimpleNamespace(id="mgr", child_agents=kids)
+    dg = TaskDelegator(mgr)
+    for r in g["agents"]:
+        for j in range(r["active_delegations"]):
+            dg.active_delegations[f"{r['id']}-d{j}"] = {"agent_id": r["id"]}
+    got = asyncio.run(dg._find_best_agents(g["tasks"]))
+    assert [a.id if a is not None else None for a in got] == [r["agent"] for r in g["delegator"]]
+
+
+def test_enhanced_memory_dropin_semantics(torch_cuda):
+    from pilottai_b200 import EnhancedMemory, MemoryItem
+
+    async def scenario():
+        mem = EnhancedMemory(max_size=50, dim=128)
+        assert await mem.semantic_search("anything") == []                 # empty store: no crash
+        with pytest.raises(ValueError, match="Text cannot be empty"):
+            await mem.store_semantic("")
+        with pytest.raises(ValueError, match="Query cannot be empty"):
+            await mem.semantic_search("")
+        with pytest.raises(ValueError, match="Failed to store content"):
+            await mem.store_semantic("x", priority=-1)                     # MemoryItem validation (ge=0)
+        for i in range(80):                                                # ring: 80 into 50
+            await mem.store_semantic(f"document number {i} about topic {i % 7}", metadata={"i": i},
+                                     tags={"even" if i % 2 == 0 else "odd", f"t{i % 3}"}, priority=i % 4)
+        assert len(mem) == 50
+        hit = await mem.semantic_search("document number 63 about topic 0", limit=1)
+        assert isinstance(hit[0], MemoryItem) and hit[0].metadata["i"] == 63
+        assert await mem.semantic_search("document number 5 about topic 5", limit=1, order="score") != [] \
+            and (await mem.semantic_search("document number 5 about topic 5", limit=50))[0].metadata["i"] >= 30  # evicted
+        res = await mem.semantic_search("document about topic", tags={"even", "t0"}, min_priority=2, limit=50)
+        assert res and all(("even" in r.tags and "t0" in r.tags and r.priority >= 2 and r.metadata["i"] >= 30) for r in res)
+        want = sorted((i for i in range(30, 80) if i % 2 == 0 and i % 3 == 0 and i % 4 >= 2))
+        assert sorted(r.metadata["i"] for r in res) == want               # filters exact after overflow
+        keys = [(-r.priority, r.timestamp) for r in res]
+        assert keys == sorted(keys)                                        # reference ordering (:114)
+        assert await mem.semantic_search("document", tags={"never-stored"}) == []
+        # expiry: ttl in the past -> filtered at query time, dropped by cleanup()
+        await mem.store_semantic("short lived note", ttl=-5, metadata={"i": "x"})
+        assert all(r.metadata["i"] != "x" for r in await mem.semantic_search("short lived note", limit=50))
+        n_before = len(mem)
+        await mem.cleanup()
+        assert len(mem) == n_before - 1
+        hit = await mem.semantic_search("document number 79 about topic 2", limit=1)
+        assert hit[0].metadata["i"] == 79                                  # host/device still aligned
+        # batched vector API
+        rng = np.random.default_rng(0)
+        emb = rng.standard_normal((10, 128)).astype(np.float32)
+        first = await mem.store_semantic_batch([f"vec {i}" for i in range(10)], emb)
+        idx, sc = await mem.semantic_search_batch(emb[[3, 7]], k=2)
+        assert idx[0, 0] == first + 3 and idx[1, 0] == first + 7 and np.allclose(sc[:, 0], 1.0, atol=1e-3)
+        mem.clear()
+        assert len(mem) == 0 and await mem.semantic_search("document") == []
+        # the other stores keep their contracts
+        await mem.store_task("t1", {"type": "a"}); await mem.store_pattern("p", 5)
+        assert (await mem.get_recent_tasks(task_type="a"))[0]["data"]["type"] == "a" and await mem.get_pattern("p") == 5
+        mem.close()
+    asyncio.run(scenario())

@@ -1,0 +1,85 @@
+"""GPU tests of the sharded path: the merge kernel (K6) on one GPU, and -- when the box has
+two or more GPUs -- the full NCCL path (one process per GPU) against the CPU oracle."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+from oracle import retrieval_c
+from oracle.retrieval_oracle import OracleStore
+from pilottai_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    torch = pytest.importorskip("torch")
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    return torch
+
+
+def test_topk_merge_kernel_matches_host_rule(torch_cuda):
+    torch = torch_cuda
+    from pilottai_b200.store import topk_merge
+    rng = np.random.default_rng(0)
+    shards, nq, k = 8, 300, 10
+    sc = np.round(rng.standard_normal((shards, nq, k)), 1)            # coarse -> many score ties
+    idx = rng.permutation(shards * nq * k).reshape(shards, nq, k).astype(np.int64)
+    sc = -np.sort(-sc, axis=2)
+    pad = rng.random((shards, nq, k)) < 0.15                          # ragged shards
+    pad = np.sort(pad, axis=2)
+    idx[pad], sc[pad] = -1, -np.inf
+    pad[:, 5] = True; idx[:, 5] = -1; sc[:, 5] = -np.inf              # a query with no result anywhere
+    gi, gs, gs64 = topk_merge(torch.from_numpy(idx).cuda(), torch.from_numpy(sc).cuda())
+    gi, gs64 = gi.cpu().numpy(), gs64.cpu().numpy()
+    for q in range(nq):
+        ci, cs = idx[:, q].ravel(), sc[:, q].ravel()
+        ok = ci >= 0
+        order = np.lexsort((ci[ok], -cs[ok]))[:k]
+        want_i = np.full(k, -1, np.int64); want_s = np.full(k, -np.inf)
+        want_i[: order.size], want_s[: order.size] = ci[ok][order], cs[ok][order]
+        assert np.array_equal(gi[q], want_i) and np.array_equal(gs64[q], want_s)
+
+
+def _worker(rank, world, port, n, dim, nq, k, out):
+    import torch
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    from pilottai_b200.sharded import ShardedSemanticStore
+    x = synth.corpus(n, dim, seed=3, dup_frac=0.01)
+    prio, tag, exp = synth.metadata(n, seed=5)
+    q = torch.from_numpy(synth.queries(nq, dim, seed=4)).cuda()
+    st = ShardedSemanticStore(dim, n, rank, world, rank)
+    for lo in range(0, n, 7000):
+        hi = min(n, lo + 7000)
+        st.append(x[lo:hi], prio[lo:hi], tag[lo:hi], exp[lo:hi])
+    idx, sc, sc64, inexact = st.search(q, k, min_priority=1, now_us=1_000_000)
+    torch.cuda.synchronize()
+    assert int(inexact.item()) == 0
+    if rank == 0:
+        np.save(out + "_i.npy", idx.cpu().numpy()); np.save(out + "_s.npy", sc64.cpu().numpy())
+    st.close()
+    dist.destroy_process_group()
+
+
+def test_nccl_sharded_search_equals_single_store(torch_cuda, tmp_path):
+    torch = torch_cuda
+    world = min(torch.cuda.device_count(), 4)
+    if world < 2:
+        pytest.skip("needs two or more GPUs")
+    import torch.multiprocessing as mp
+    n, dim, nq, k = 30_000, 256, 64, 10
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    out = str(tmp_path / "merged")
+    mp.spawn(_worker, args=(world, port, n, dim, nq, k, out), nprocs=world, join=True)
+    whole = OracleStore(dim, n)
+    prio, tag, exp = synth.metadata(n, seed=5)
+    whole.append(synth.corpus(n, dim, seed=3, dup_frac=0.01), prio, tag, exp)
+    wi, ws = retrieval_c.search(whole, synth.queries(nq, dim, seed=4), k, min_priority=1, now_us=1_000_000)
+    assert np.array_equal(np.load(out + "_i.npy"), wi)
+    assert np.array_equal(np.load(out + "_s.npy"), ws)
