@@ -218,6 +218,7 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
     a.nslots = h->count; a.capacity = h->capacity; a.head = h->head; a.ld = h->ld;
     a.dbg = h->opt_dbg;
     CUtensorMap map_q, map_c;
+    pilott::FinishArgs f{};
     int lists = 0;
     a.list_len = 32;
     if (kern != 1) {
@@ -226,9 +227,13 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
         if (rc) return rc;
         if (cg == 1) map_c = h->map_c;
         else { rc = encode_map(&map_c, h->vec, h->capacity, h->ld, 128); if (rc) return rc; }
-        a.slots = pilott::scan_tc_slots(nq, h->count, cg, ctas);
-        a.list_len = (h->opt_list_len == 16 || (h->opt_list_len == 0 && k <= 12)) ? 16 : 32;
-        lists = a.slots * pilott::scan_tc_lists_per_slot();
+        a.slots = pilott::scan_tc_slots(nq, h->count, cg, ctas, &a.slots_rem);
+        a.list_len = ((h->opt_list_len == 16 && k <= 16) || (h->opt_list_len == 0 && k <= 12)) ? 16 : 32;
+        lists = (a.slots + (a.slots_rem > 0 ? 1 : 0)) * pilott::scan_tc_lists_per_slot();
+        f.rows_per_group = pilott::scan_tc_rows_per_group(cg);
+        f.lists_base = a.slots * pilott::scan_tc_lists_per_slot();
+        f.groups_rem = a.slots_rem;
+        f.lists_extra = pilott::scan_tc_lists_per_slot();
         rc = h->partials.ensure((size_t)nq * lists * KP_HOST * 8);
         if (rc) return rc;
         a.partials = (uint64_t*)h->partials.p;
@@ -244,6 +249,7 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
     } else {
         a.slots = pilott::scan_generic_slots(nq, h->count, h->num_sms);
         lists = a.slots;
+        f.rows_per_group = 1; f.lists_base = lists; f.groups_rem = 0; f.lists_extra = 0;
         rc = h->partials.ensure((size_t)nq * lists * KP_HOST * 8);
         if (rc) return rc;
         a.partials = (uint64_t*)h->partials.p;
@@ -254,7 +260,6 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
         if (e1) CK(cudaEventRecord(e1, st));
     }
     if (out_inexact) CK(cudaMemsetAsync(out_inexact, 0, 4, st));
-    pilott::FinishArgs f{};
     f.partials = a.partials; f.slots = lists; f.list_len = a.list_len; f.qb = h->qbuf.p; f.vec = h->vec; f.ld = h->ld;
     f.nq = nq; f.capacity = h->capacity; f.head = h->head; f.base_seq = h->total - h->count;
     f.k = k; f.seq_mul = h->seq_mul; f.seq_add = h->seq_add;

@@ -39,9 +39,51 @@ __device__ __forceinline__ double exact_cosine(const __nv_bfloat16* __restrict__
                                                const __nv_bfloat16* __restrict__ mrow, int ld,
                                                double* nq_out = nullptr) {
     double dot = 0.0, nq = 0.0, nm = 0.0;
+    for (int c = 0; c < ld; c += 32) {          // ld is a multiple of 64; 8 loads in flight per step
+        uint4 qv[4], mv[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            qv[u] = __ldg(reinterpret_cast<const uint4*>(qrow + c + 8 * u));
+            mv[u] = __ldg(reinterpret_cast<const uint4*>(mrow + c + 8 * u));
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const uint32_t qw[4] = {qv[u].x, qv[u].y, qv[u].z, qv[u].w}, mw[4] = {mv[u].x, mv[u].y, mv[u].z, mv[u].w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const double q0 = (double)__uint_as_float(qw[j] << 16);
+                const double q1 = (double)__uint_as_float(qw[j] & 0xffff0000u);
+                const double m0 = (double)__uint_as_float(mw[j] << 16);
+                const double m1 = (double)__uint_as_float(mw[j] & 0xffff0000u);
+                dot = __fma_rn(q0, m0, dot); nq = __fma_rn(q0, q0, nq); nm = __fma_rn(m0, m0, nm);
+                dot = __fma_rn(q1, m1, dot); nq = __fma_rn(q1, q1, nq); nm = __fma_rn(m1, m1, nm);
+            }
+        }
+    }
+    if (nq_out) *nq_out = nq;
+    const double den = __dmul_rn(__dsqrt_rn(nq), __dsqrt_rn(nm));
+    return den > 0.0 ? __ddiv_rn(dot, den) : 0.0;
+}
+
+// Sorts a bitonic sequence (one key per lane) into descending order: 5 compare-exchange steps.
+__device__ __forceinline__ uint64_t warp_bitonic_merge_desc(uint64_t v, int lane) {
+#pragma unroll
+    for (int j = 16; j > 0; j >>= 1) {
+        const uint64_t o = shfl_xor64(v, j);
+        const bool lower = (lane & j) == 0;
+        const uint64_t mn = v < o ? v : o, mx = v < o ? o : v;
+        v = lower ? mx : mn;
+    }
+    return v;
+}
+
+// Same arithmetic as exact_cosine, operands staged in shared memory (generic pointers).
+__device__ __forceinline__ double exact_cosine_smem(const unsigned char* qrow, const unsigned char* mrow,
+                                                    int ld, double* nq_out) {
+    double dot = 0.0, nq = 0.0, nm = 0.0;
     for (int c = 0; c < ld; c += 8) {
-        const uint4 qv = __ldg(reinterpret_cast<const uint4*>(qrow + c));
-        const uint4 mv = __ldg(reinterpret_cast<const uint4*>(mrow + c));
+        const uint4 qv = *reinterpret_cast<const uint4*>(qrow + 2 * c);
+        const uint4 mv = *reinterpret_cast<const uint4*>(mrow + 2 * c);
         const uint32_t qw[4] = {qv.x, qv.y, qv.z, qv.w}, mw[4] = {mv.x, mv.y, mv.z, mv.w};
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -53,51 +95,114 @@ __device__ __forceinline__ double exact_cosine(const __nv_bfloat16* __restrict__
             dot = __fma_rn(q1, m1, dot); nq = __fma_rn(q1, q1, nq); nm = __fma_rn(m1, m1, nm);
         }
     }
-    if (nq_out) *nq_out = nq;
+    *nq_out = nq;
     const double den = __dmul_rn(__dsqrt_rn(nq), __dsqrt_rn(nm));
     return den > 0.0 ? __ddiv_rn(dot, den) : 0.0;
 }
 
-// One warp per query.
-__global__ void __launch_bounds__(128)
-finish_kernel(const uint64_t* __restrict__ partials, int slots, int list_len,
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src) : "memory");
+}
+
+constexpr int FIN_WARPS = 4;      // warps per query in finish_kernel
+constexpr int FIN_MAXLOADS = 8;   // 32-entry loads each warp prefetches at once
+
+// One CTA (4 warps) per query.  Warps merge disjoint subsets of the candidate lists in
+// parallel (all their loads issued up front), warp 0 merges the four pools, re-scores the
+// survivors exactly and writes the result.
+__global__ void __launch_bounds__(FIN_WARPS * 32)
+finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_len, int rows_per_group,
+              int lists_base, int groups_rem, int lists_extra,
               const __nv_bfloat16* __restrict__ qb,
               const __nv_bfloat16* __restrict__ vec, int ld, int64_t nq, int64_t capacity,
               int64_t head, int64_t base_seq, int64_t seq_mul, int64_t seq_add, int k, double err,
               int64_t* __restrict__ out_idx,
               float* __restrict__ out_score, double* __restrict__ out_score64,
-              uint8_t* __restrict__ flags, int32_t* __restrict__ inexact) {
-    const int lane = threadIdx.x & 31;
-    const int64_t q = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (q >= nq) return;
-    // 1. top-KP of all lists' candidates by approximate key.  `bound` = best key any list may
-    //    have dropped: a FULL list (all list_len entries used) may have dropped rows no better
-    //    than its own worst entry; the merged pool, if full, dropped rows no better than its worst.
+              uint8_t* __restrict__ flags, int32_t* __restrict__ inexact, int stage_rows) {
+    extern __shared__ __align__(16) unsigned char s_rows[];     // [pool_n + 1][ld*2 + 16] when stage_rows
+    __shared__ uint64_t s_pool[FIN_WARPS][32];
+    __shared__ uint64_t s_bound[FIN_WARPS];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t q = blockIdx.x;
+    // 1. top-KP of this warp's lists by approximate key.  `bound` = best key any list may have
+    //    dropped: a FULL list (all list_len entries used) may have dropped rows no better than
+    //    its own worst entry; the merged pool, if full, dropped rows no better than its worst.
     const int per_load = 32 / list_len;                    // lists fetched per 32-lane load (1 or 2)
-    const uint64_t* p = partials + q * (int64_t)slots * list_len;
+    const int slots = lists_base + ((q / rows_per_group) < groups_rem ? lists_extra : 0);   // lists this query has
+    const uint64_t* p = partials + q * (int64_t)slots_alloc * list_len;
     const int nloads = (slots + per_load - 1) / per_load;
     uint64_t best = 0ull, bound = 0ull;
-    for (int i = 0; i < nloads; ++i) {
-        const int li = i * per_load + lane / list_len;     // list this lane reads from
-        uint64_t x = li < slots ? p[(int64_t)li * list_len + (lane % list_len)] : 0ull;
-        uint64_t mn = x;                                   // per-list minimum (segmented butterfly)
-        for (int j = list_len / 2; j > 0; j >>= 1) {
-            const uint64_t o = shfl_xor64(mn, j);
-            mn = mn < o ? mn : o;
+    for (int i0 = warp; i0 < nloads; i0 += FIN_WARPS * FIN_MAXLOADS) {
+        uint64_t x[FIN_MAXLOADS];
+#pragma unroll
+        for (int u = 0; u < FIN_MAXLOADS; ++u) {           // all loads in flight before any sort
+            const int i = i0 + u * FIN_WARPS;
+            const int li = i * per_load + lane / list_len; // list this lane reads from
+            x[u] = (i < nloads && li < slots) ? __ldcg(p + (int64_t)li * list_len + (lane % list_len)) : 0ull;
         }
-        if (mn != 0ull && mn > bound) bound = mn;          // list is full: it may have dropped rows <= mn
-        x = warp_sort64<false>(x, lane);
-        best = warp_sort64<true>(best > x ? best : x, lane);
+#pragma unroll
+        for (int u = 0; u < FIN_MAXLOADS; ++u) {
+            if (i0 + u * FIN_WARPS >= nloads) break;
+            uint64_t mn = x[u];                            // per-list minimum (segmented butterfly)
+            for (int j = list_len / 2; j > 0; j >>= 1) {
+                const uint64_t o = shfl_xor64(mn, j);
+                mn = mn < o ? mn : o;
+            }
+            if (mn != 0ull && mn > bound) bound = mn;      // list is full: it may have dropped rows <= mn
+            const uint64_t xs = warp_sort64<false>(x[u], lane);
+            best = warp_bitonic_merge_desc(best > xs ? best : xs, lane);
+        }
     }
 #pragma unroll
     for (int j = 16; j > 0; j >>= 1) {
         const uint64_t o = shfl_xor64(bound, j);
         bound = bound > o ? bound : o;
     }
-    const uint64_t worst = shfl64(best, 31);
+    s_pool[warp][lane] = best;
+    if (lane == 0) s_bound[warp] = bound;
+    __syncthreads();
+    // 2. merge the four pools (each sorted descending; read reversed = ascending)
+    if (warp == 0) {
+#pragma unroll
+        for (int w = 1; w < FIN_WARPS; ++w) {
+            const uint64_t xs = s_pool[w][31 - lane];
+            best = warp_bitonic_merge_desc(best > xs ? best : xs, lane);
+            if (s_bound[w] > bound) bound = s_bound[w];
+        }
+    }
+    // The pool that gets re-scored is as large as one candidate list (16 when k <= 12, else 32).
+    const int pool_n = list_len;
+    if (lane >= pool_n) best = 0ull;
+    const size_t row_bytes = (size_t)ld * 2 + 16;           // +16: rows start on different bank groups
+    if (stage_rows) {
+        // 2b. all four warps copy the 32 surviving rows (and the query) into shared memory with
+        //     16-byte async copies, so the sequential fp64 chains below never wait on HBM.
+        __syncthreads();
+        if (warp == 0) s_pool[0][lane] = best;
+        __syncthreads();
+        const int chunks = ld / 8;                          // 16-byte pieces per row
+        for (int r = warp; r <= pool_n; r += FIN_WARPS) {
+            const __nv_bfloat16* src;
+            if (r == pool_n) src = qb + q * ld;
+            else {
+                const uint64_t key = s_pool[0][r];
+                if (key == 0ull) continue;
+                int64_t slot = head + key_age(key);
+                if (slot >= capacity) slot -= capacity;
+                src = vec + slot * ld;
+            }
+            for (int c = lane; c < chunks; c += 32) cp_async16(s_rows + r * row_bytes + 16 * c, src + 8 * c);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncthreads();
+    }
+    if (warp != 0) return;
+    const uint64_t worst = shfl64(best, pool_n - 1);
     if (worst != 0ull && worst > bound) bound = worst;     // the pool itself is full
     const bool pool_full = bound != 0ull;                  // something may have been dropped
-    // 2. exact re-score
+    // 3. exact re-score
     const bool valid = best != 0ull;
     double sc = -INFINITY;
     int64_t seq = INT64_MAX;
@@ -107,10 +212,11 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots, int list_len,
         const uint32_t age = key_age(best);
         int64_t slot = head + age;
         if (slot >= capacity) slot -= capacity;
-        sc = exact_cosine(qrow, vec + slot * ld, ld, &nqn);
+        sc = stage_rows ? exact_cosine_smem(s_rows + pool_n * row_bytes, s_rows + lane * row_bytes, ld, &nqn)
+                        : exact_cosine(qrow, vec + slot * ld, ld, &nqn);
         seq = base_seq + age;
     }
-    // 3. final order
+    // 4. final order
     warp_sort_pairs(sc, seq, lane);
     if (lane < k) {
         const bool ok = seq != INT64_MAX;
@@ -118,7 +224,7 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots, int list_len,
         out_score[q * k + lane] = ok ? (float)sc : -INFINITY;
         if (out_score64) out_score64[q * k + lane] = ok ? sc : -INFINITY;
     }
-    // 4. gap check: every row dropped by the approximate pass has approximate score <=
+    // 5. gap check: every row dropped by the approximate pass has approximate score <=
     // the worst kept one; it cannot reach the exact k-th score if the gap exceeds err.
     const double e_k = __longlong_as_double((long long)shfl64((uint64_t)__double_as_longlong(sc), k - 1));
     if (lane == 0) {
@@ -134,11 +240,18 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots, int list_len,
 
 cudaError_t launch_finish(const FinishArgs& a, cudaStream_t st) {
     if (a.nq <= 0) return cudaSuccess;
-    const int wpb = 4;
-    finish_kernel<<<(unsigned)((a.nq + wpb - 1) / wpb), wpb * 32, 0, st>>>(
-        a.partials, a.slots, a.list_len, (const __nv_bfloat16*)a.qb, (const __nv_bfloat16*)a.vec, a.ld, a.nq,
+    // stage the surviving rows in shared memory when they fit (list_len + 1 rows of ld*2+16 bytes)
+    const size_t smem = (size_t)(a.list_len + 1) * ((size_t)a.ld * 2 + 16);
+    const int stage_rows = smem <= 100 * 1024 ? 1 : 0;
+    if (stage_rows) {
+        cudaError_t e = cudaFuncSetAttribute(finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    finish_kernel<<<(unsigned)a.nq, FIN_WARPS * 32, stage_rows ? smem : 0, st>>>(
+        a.partials, a.slots, a.list_len, a.rows_per_group, a.lists_base, a.groups_rem, a.lists_extra,
+        (const __nv_bfloat16*)a.qb, (const __nv_bfloat16*)a.vec, a.ld, a.nq,
         a.capacity, a.head, a.base_seq, a.seq_mul, a.seq_add, a.k, a.err, a.out_idx, a.out_score, a.out_score64,
-        a.flags, a.inexact);
+        a.flags, a.inexact, stage_rows);
     return cudaGetLastError();
 }
 

@@ -17,7 +17,8 @@ struct ScanArgs {
     int64_t capacity;
     int64_t head;            // physical slot of the oldest row
     int ld;                  // row stride in elements (multiple of 64)
-    int slots;               // partial lists per query
+    int slots;               // work units per query group (base count)
+    int slots_rem;           // this many groups (the first ones) get one more unit
     int list_len;            // candidates per list the scan writes (16 or 32)
     int dbg;                 // developer switches for the tcgen05 kernel (0 in production)
 };
@@ -29,7 +30,8 @@ int scan_generic_slots(int64_t nq, int64_t nslots, int num_sms);
 // tcgen05 scan.  cg = 1 or 2.
 cudaError_t launch_scan_tc(const ScanArgs& a, const CUtensorMap* map_q, const CUtensorMap* map_c,
                            int cg, int ctas, cudaStream_t st);
-int scan_tc_slots(int64_t nq, int64_t nslots, int cg, int ctas);
+int scan_tc_slots(int64_t nq, int64_t nslots, int cg, int ctas, int* rem);
+int scan_tc_rows_per_group(int cg);
 int scan_tc_lists_per_slot();   // candidate lists each (query, slot) writes; partials hold slots*this lists
 cudaError_t scan_tc_init();   // opt-in shared memory attributes
 
@@ -44,7 +46,8 @@ cudaError_t launch_scale(const float* inv_norm, const int32_t* prio, const uint6
                          uint64_t req, int64_t now_us, float* scale, cudaStream_t st);
 
 struct FinishArgs {
-    const uint64_t* partials; int slots; int list_len;
+    const uint64_t* partials; int slots; int list_len;   // slots = allocated lists per query
+    int rows_per_group, lists_base, groups_rem, lists_extra;  // lists of query q: lists_base + (q/rows_per_group < groups_rem ? lists_extra : 0)
     const void* qb; const void* vec; int ld;
     int64_t nq, capacity, head, base_seq;
     int k; double err;
