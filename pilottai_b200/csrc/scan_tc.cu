@@ -19,6 +19,8 @@
 // epilogue time, so with two stages the epilogue of one tile must fit in one MMA time), and
 // every SM sub-partition holds two epilogue warps that cover each other's latencies.
 // Pipelines: smem full/empty ring (TMA <-> MMA), TMEM full/empty x2 (MMA <-> epilogue).
+#include <cstdio>
+
 #include "common.cuh"
 #include "internal.h"
 
@@ -33,6 +35,7 @@ constexpr int ACC_STAGES = 2;  // 2 x 256 TMEM columns
 constexpr int EPI_SETS = 2;    // one per accumulator stage
 constexpr int CAPT = 46;       // per-row candidate buffer: KP survivors + pending appends (smem budget)
 constexpr int TC_THREADS = 128 + EPI_SETS * 128;
+constexpr int PF_TILES = 0;     // corpus tiles prefetched into L2 ahead of the TMA loads (0: off -- measured no gain)
 constexpr int SC_RING = 4;     // staged scale tiles in flight (full/empty mbarrier pair per slot)
 
 template <int CG> struct TcCfg {
@@ -100,6 +103,11 @@ __device__ __forceinline__ void tma_load_2d_cg2(uint32_t dst, const CUtensorMap*
     asm volatile(
         "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
         ::"r"(dst), "l"(map), "r"(bar_cluster), "r"(c0), "r"(c1) : "memory");
+}
+
+// Pull a tile of a tensor map into L2 ahead of its TMA load (no shared-memory destination).
+__device__ __forceinline__ void tma_prefetch_l2_2d(const CUtensorMap* map, int c0, int c1) {
+    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];" ::"l"(map), "r"(c0), "r"(c1) : "memory");
 }
 
 // 1-D bulk copy global -> shared, completion counted on a CTA-local mbarrier.
@@ -177,7 +185,14 @@ __device__ __forceinline__ void tmem_ld16_issue(uint32_t taddr, uint32_t (&v)[16
           "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
         : "r"(taddr) : "memory");
 }
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// Waits for every tcgen05.ld this thread issued.  The registers are passed as read-write operands
+// so the compiler cannot move their consumers above the wait.
+__device__ __forceinline__ void tmem_ld_wait(uint32_t (&v)[16]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]),
+                   "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15])
+                 :: "memory");
+}
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
@@ -277,6 +292,8 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                     }
                     const uint32_t sa = stage_base + stage * Cfg::STAGE_BYTES;
                     const uint32_t sb = sa + Cfg::A_BYTES;
+                    // corpus k-block of the tile PF_TILES ahead -> L2, so its TMA load later sees L2 latency
+                    if (PF_TILES > 0 && !(dbg & 8) && t + PF_TILES < t_hi) tma_prefetch_l2_2d(&map_c, kb * BK, n0 + PF_TILES * BN);
                     if (CG == 1) {
                         mbar_arrive_expect_tx(bar_full + 8 * stage, Cfg::STAGE_BYTES);
                         tma_load_2d(sa, &map_q, kb * BK, (int)q0, bar_full + 8 * stage);
@@ -297,12 +314,17 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
             constexpr uint32_t idesc = make_idesc(BM * CG, BN);
             int stage = 0; uint32_t phase = 0;
             int as = 0; uint32_t aphase = 0;
+            long long w_tempty = 0, w_full = 0, t_start = clock64();
             for (int64_t t = t_lo; t < t_hi; ++t) {
+                long long c0 = (dbg & 4) ? clock64() : 0;
                 mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
+                if (dbg & 4) w_tempty += clock64() - c0;
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + as * BN;
                 for (int kb = 0; kb < kblocks; ++kb) {
+                    c0 = (dbg & 4) ? clock64() : 0;
                     mbar_wait(bar_full + 8 * stage, phase);
+                    if (dbg & 4) w_full += clock64() - c0;
                     tc_fence_after();
                     const uint32_t sa = stage_base + stage * Cfg::STAGE_BYTES;
                     const uint64_t adesc = make_desc(sa), bdesc = make_desc(sa + Cfg::A_BYTES);
@@ -317,6 +339,9 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                 umma_commit<CG>(bar_tfull + 8 * as);              // accumulator tile complete
                 if (++as == ACC_STAGES) { as = 0; aphase ^= 1; }
             }
+            if ((dbg & 4) && (blockIdx.x == 0 || blockIdx.x == 70))
+                printf("[mma cta %d] total %lld cyc, wait accumulator-free %lld, wait smem-full %lld, tiles %d\n",
+                       (int)blockIdx.x, clock64() - t_start, w_tempty, w_full, (int)(t_hi - t_lo));
         }
         __syncwarp();
     } else if (warp >= 4) {
@@ -333,6 +358,9 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
         const bool has_q = qrow < nq;
         uint32_t aphase = 0;
         int as = 0;
+        long long w_tfull = 0, t_start = clock64();
+        int n_prune = 0, n_slow = 0;
+        long long t_prune = 0, t_slow = 0, t_loop = 0;
         constexpr int CPS = BN / EPI_SETS;                         // columns per set
         for (int64_t t = t_lo; t < t_hi; ++t) {
             const uint32_t n0 = (uint32_t)(t * BN);
@@ -341,45 +369,37 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
             const uint32_t g = has_q ? __ldcg(gthr + qrow) : 0u;
             const int64_t ti = t - t_lo;
             const float* scb = ssc + (ti % SC_RING) * BN;
+            const long long c0 = (dbg & 4) ? clock64() : 0;
             mbar_wait(bar_scfull + 8 * (int)(ti % SC_RING), (uint32_t)((ti / SC_RING) & 1));
             mbar_wait(bar_tfull + 8 * as, aphase);
+            if (dbg & 4) w_tfull += clock64() - c0;
             tc_fence_after();
             if (g > f2ord(thr)) thr = ord2f(g);
             const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
-#pragma unroll 1
-            for (int c = set * CPS; c < ((dbg & 1) ? 0 : (set + 1) * CPS); c += 16) {
-                uint32_t v[16];
-                tmem_ld16_issue(taddr0 + c, v);
-                float sc[16];
+            // One 16-column chunk: scale, test groups of 4 (one FMNMX tree + compare + vote per group;
+            // fmaxf drops NaN = filtered rows), append on the rare hit, prune full rows.
+            auto process = [&](const uint32_t (&v)[16], const float (&sc)[16], const int c) {
+                float s[16];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const float4 f = *reinterpret_cast<const float4*>(scb + c + 4 * j);   // broadcast LDS.128
-                    sc[4 * j] = f.x; sc[4 * j + 1] = f.y; sc[4 * j + 2] = f.z; sc[4 * j + 3] = f.w;
-                }
-                tmem_ld_wait();
-                if (dbg & 2) { if (v[0] == 0x7fc12345u && v[15] == 0x7fc54321u) thr = 1.f; continue; }
-                // Test groups of 4: one FMNMX tree + compare + vote per group.  fmaxf drops NaN
-                // (filtered rows), so a fully filtered group compares NaN >= thr == false.
-                bool touched = false;
+                for (int j = 0; j < 16; ++j) s[j] = __uint_as_float(v[j]) * sc[j];
+                float mx[4];
 #pragma unroll
-                for (int g0 = 0; g0 < 16; g0 += 4) {
-                    const float s0 = __uint_as_float(v[g0]) * sc[g0];
-                    const float s1 = __uint_as_float(v[g0 + 1]) * sc[g0 + 1];
-                    const float s2 = __uint_as_float(v[g0 + 2]) * sc[g0 + 2];
-                    const float s3 = __uint_as_float(v[g0 + 3]) * sc[g0 + 3];
-                    const float mx = fmaxf(fmaxf(s0, s1), fmaxf(s2, s3));
-                    if (__any_sync(FULL, mx >= thr)) {
-                        // slow path (warp-uniform entry): append the survivors of this group
-                        touched = true;
-                        const float s4[4] = {s0, s1, s2, s3};
+                for (int g = 0; g < 4; ++g) mx[g] = fmaxf(fmaxf(s[4 * g], s[4 * g + 1]), fmaxf(s[4 * g + 2], s[4 * g + 3]));
+                // level 1: one vote for the whole chunk (the common case is "nothing to do")
+                if (!__any_sync(FULL, fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) >= thr)) return;
+                const long long cs = (dbg & 4) ? clock64() : 0;
+                // level 2 (warp-uniform entry): per group of 4, append the survivors
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                    if (__any_sync(FULL, mx[g] >= thr)) {
+                        if (dbg & 4) ++n_slow;
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
-                            if (s4[j] >= thr)
-                                mine[cnt++] = ((uint64_t)f2ord(s4[j]) << 32) | (n0 + c + g0 + j);
+                            if (s[4 * g + j] >= thr)
+                                mine[cnt++] = ((uint64_t)f2ord(s[4 * g + j]) << 32) | (n0 + c + 4 * g + j);
                         }
                     }
-                    if (KPT == 32 && (g0 & 4) && touched) {    // 32-entry lists: fullness check every 8
-                        touched = false;
+                    if (KPT == 32 && (g & 1)) {                // 32-entry lists: fullness check every 8
                         const unsigned full = __ballot_sync(FULL, cnt > CAPT - 8);
                         if (full) {
                             warp_prune_rows<CAPT, KPT>(full, rows, lane, cnt, conv, thr, head32, cap32);
@@ -387,14 +407,45 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                         }
                     }
                 }
-                if (KPT == 16 && touched) {                    // 16-entry lists: once per 16 columns
+                if (dbg & 4) t_slow += clock64() - cs;
+                if (KPT == 16) {                               // 16-entry lists: once per 16 columns
                     const unsigned full = __ballot_sync(FULL, cnt > CAPT - 16);
                     if (full) {
+                        const long long cp = (dbg & 4) ? clock64() : 0;
                         warp_prune_rows<CAPT, KPT>(full, rows, lane, cnt, conv, thr, head32, cap32);
                         if (((full >> lane) & 1u) && has_q) atomicMax(gthr + qrow, f2ord(thr));
+                        if (dbg & 4) { n_prune += __popc(full); t_prune += clock64() - cp; }
                     }
                 }
+            };
+            auto load_scale = [&](float (&sc)[16], const int c) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float4 f = *reinterpret_cast<const float4*>(scb + c + 4 * j);   // broadcast LDS.128
+                    sc[4 * j] = f.x; sc[4 * j + 1] = f.y; sc[4 * j + 2] = f.z; sc[4 * j + 3] = f.w;
+                }
+            };
+            // Software pipeline over the set's 128 columns: the TMEM load of the next chunk is in
+            // flight while the current one is processed (two register buffers, ping-pong).
+            const long long cl = (dbg & 4) ? clock64() : 0;
+            if (!(dbg & 1)) {
+                uint32_t va[16], vb[16];
+                float sa[16], sb[16];
+                const int c_lo = set * CPS, c_hi = (set + 1) * CPS;
+                tmem_ld16_issue(taddr0 + c_lo, va);
+                load_scale(sa, c_lo);
+#pragma unroll 1
+                for (int c = c_lo; c < c_hi; c += 32) {
+                    tmem_ld_wait(va);
+                    tmem_ld16_issue(taddr0 + c + 16, vb);
+                    load_scale(sb, c + 16);
+                    if (!(dbg & 2)) process(va, sa, c);
+                    tmem_ld_wait(vb);
+                    if (c + 32 < c_hi) { tmem_ld16_issue(taddr0 + c + 32, va); load_scale(sa, c + 32); }
+                    if (!(dbg & 2)) process(vb, sb, c + 16);
+                }
             }
+            if (dbg & 4) t_loop += clock64() - cl;
             // release this accumulator stage to the MMA issuer (in the leader CTA)
             tc_fence_before();
             __syncwarp();
@@ -405,6 +456,9 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
             }
             if (++as == ACC_STAGES) { as = 0; aphase ^= 1; }
         }
+        if ((dbg & 4) && lane == 0 && (blockIdx.x == 0 || blockIdx.x == 70) && (warp == 4 || warp == 9))
+            printf("[epi cta %d warp %d] total %lld cyc, wait accumulator-full %lld, column loop %lld (slow path %lld in %d groups, prune %lld for %d rows)\n",
+                   (int)blockIdx.x, warp, clock64() - t_start, w_tfull, t_loop, t_slow, n_slow, t_prune, n_prune);
         // flush: final prune of every row, write this (slot, set) candidate list
         __syncwarp();
         for (int r = 0; r < 32; ++r) {
