@@ -124,6 +124,7 @@ struct pilott_mem {
     uint64_t* tagmask = nullptr;
     int64_t* expires = nullptr;
     float* scale = nullptr;
+    float* tile_max = nullptr;
     DevBuf qbuf, partials, gthr, exact_scratch, stage_dev, result_dev, misc_dev;
     HostBuf stage_host;
     cudaStream_t own_stream = nullptr;
@@ -146,9 +147,9 @@ int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
 
 void free_columns(pilott_mem* h) {
     cudaFree(h->vec); cudaFree(h->inv_norm); cudaFree(h->prio); cudaFree(h->tagmask);
-    cudaFree(h->expires); cudaFree(h->scale);
+    cudaFree(h->expires); cudaFree(h->scale); cudaFree(h->tile_max);
     h->vec = nullptr; h->inv_norm = nullptr; h->prio = nullptr; h->tagmask = nullptr;
-    h->expires = nullptr; h->scale = nullptr;
+    h->expires = nullptr; h->scale = nullptr; h->tile_max = nullptr;
 }
 
 int alloc_columns(pilott_mem* h) {
@@ -159,6 +160,7 @@ int alloc_columns(pilott_mem* h) {
     CK(cudaMalloc(&h->tagmask, n * 8));
     CK(cudaMalloc(&h->expires, n * 8));
     CK(cudaMalloc(&h->scale, (size_t)h->cap_pad * 4));
+    CK(cudaMalloc(&h->tile_max, (size_t)(h->cap_pad / 256) * 4));
     CK(cudaMemset(h->vec, 0, n * h->ld * 2));
     CK(cudaMemset(h->inv_norm, 0, n * 4));
     CK(cudaMemset(h->prio, 0, n * 4));
@@ -208,13 +210,13 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
     if (rc) return rc;
     CK(pilott::launch_convert_queries(q_dev, nq, h->dim, h->ld, h->qbuf.p, st));
     CK(pilott::launch_scale(h->inv_norm, h->prio, h->tagmask, h->expires, h->count, h->cap_pad,
-                            min_prio, req, now_us, h->scale, st));
+                            min_prio, req, now_us, h->scale, h->tile_max, st));
     h->launches += 2;
 
     int kern = pick_kernel(h);
     const int ctas = h->opt_ctas > 0 ? h->opt_ctas : h->num_sms;
     pilott::ScanArgs a{};
-    a.qb = h->qbuf.p; a.vec = h->vec; a.scale = h->scale; a.nq = nq;
+    a.qb = h->qbuf.p; a.vec = h->vec; a.scale = h->scale; a.tile_max = h->tile_max; a.nq = nq;
     a.nslots = h->count; a.capacity = h->capacity; a.head = h->head; a.ld = h->ld;
     a.dbg = h->opt_dbg;
     CUtensorMap map_q, map_c;
@@ -598,7 +600,7 @@ int pilott_mem_compact(pilott_mem_t* h, int64_t now_us, int64_t* kept, uint8_t* 
     // gather the survivors into fresh columns, then swap
     pilott_mem old = *h;
     h->vec = nullptr; h->inv_norm = nullptr; h->prio = nullptr; h->tagmask = nullptr;
-    h->expires = nullptr; h->scale = nullptr;
+    h->expires = nullptr; h->scale = nullptr; h->tile_max = nullptr;
     rc = alloc_columns(h);
     if (rc) { free_columns(h); *h = old; return rc; }
     if (m > 0) {

@@ -10,6 +10,7 @@ struct ScanArgs {
     const void* qb;          // bf16 [nq_pad, ld] converted queries
     const void* vec;         // bf16 [capacity, ld]
     const float* scale;      // [cap_pad]: inverse norm, NaN for masked / unused slots
+    const float* tile_max;   // [cap_pad/256]: largest valid scale of each 256-row tile
     uint64_t* partials;      // [nq][slots][KP] candidate keys
     uint32_t* gthr;          // [nq] shared per-query threshold (ordered-uint score), zeroed per search
     int64_t nq;
@@ -43,7 +44,7 @@ cudaError_t launch_convert_queries(const float* q, int64_t nq, int dim, int ld, 
                                    cudaStream_t st);
 cudaError_t launch_scale(const float* inv_norm, const int32_t* prio, const uint64_t* tagmask,
                          const int64_t* expires, int64_t nslots, int64_t cap_pad, int32_t min_prio,
-                         uint64_t req, int64_t now_us, float* scale, cudaStream_t st);
+                         uint64_t req, int64_t now_us, float* scale, float* tile_max, cudaStream_t st);
 
 struct FinishArgs {
     const uint64_t* partials; int slots; int list_len;   // slots = allocated lists per query

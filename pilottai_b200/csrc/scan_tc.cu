@@ -86,6 +86,16 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
         : "=r"(ok) : "r"(bar), "r"(parity), "r"(0x4000u) : "memory");
     return ok != 0;
 }
+// Non-blocking probe of a barrier phase.
+__device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
 // Bounded wait: a protocol bug traps (launch failure) instead of hanging the GPU.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     for (uint32_t spins = 0; !mbar_try_wait(bar, parity); ++spins) {
@@ -213,8 +223,8 @@ __device__ __forceinline__ void cluster_sync_all() {
 template <int CG, int KPT>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_c,
-               const float* __restrict__ scale, uint64_t* __restrict__ partials,
-               uint32_t* __restrict__ gthr, int64_t nq, int64_t nslots, int64_t capacity, int64_t head, int kblocks, int slots, int slots_rem, int groups, int dbg) {
+               const float* __restrict__ scale, const float* __restrict__ tile_max,
+               uint64_t* __restrict__ partials, uint32_t* __restrict__ gthr, int64_t nq, int64_t nslots, int64_t capacity, int64_t head, int kblocks, int slots, int slots_rem, int groups, int dbg) {
     using Cfg = TcCfg<CG>;
     extern __shared__ unsigned char smem_dyn[];
     const uint32_t base = (smem_u32(smem_dyn) + 1023u) & ~1023u;        // 1024-B aligned (swizzle atom)
@@ -360,13 +370,15 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
         int as = 0;
         long long w_tfull = 0, t_start = clock64();
         int n_prune = 0, n_slow = 0;
-        long long t_prune = 0, t_slow = 0, t_loop = 0;
+        long long t_prune = 0, t_slow = 0, t_loop = 0, t_early = 0;
+        int n_early = 0;
         constexpr int CPS = BN / EPI_SETS;                         // columns per set
         for (int64_t t = t_lo; t < t_hi; ++t) {
             const uint32_t n0 = (uint32_t)(t * BN);
             // Any list's KPT-th best score for this query bounds the global top-KPT from below, so
             // all CTAs sweeping the same query share one monotone threshold through gthr[query].
             const uint32_t g = has_q ? __ldcg(gthr + qrow) : 0u;
+            const float smax = __ldg(tile_max + t);                 // largest valid scale in this tile
             const int64_t ti = t - t_lo;
             const float* scb = ssc + (ti % SC_RING) * BN;
             const long long c0 = (dbg & 4) ? clock64() : 0;
@@ -378,20 +390,34 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
             const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
             // One 16-column chunk: scale, test groups of 4 (one FMNMX tree + compare + vote per group;
             // fmaxf drops NaN = filtered rows), append on the rare hit, prune full rows.
-            auto process = [&](const uint32_t (&v)[16], const float (&sc)[16], const int c) {
-                float s[16];
+            auto load_scale = [&](float (&sc)[16], const int c) {
 #pragma unroll
-                for (int j = 0; j < 16; ++j) s[j] = __uint_as_float(v[j]) * sc[j];
+                for (int j = 0; j < 4; ++j) {
+                    const float4 f = *reinterpret_cast<const float4*>(scb + c + 4 * j);   // broadcast LDS.128
+                    sc[4 * j] = f.x; sc[4 * j + 1] = f.y; sc[4 * j + 2] = f.z; sc[4 * j + 3] = f.w;
+                }
+            };
+            auto process = [&](const uint32_t (&v)[16], const int c) {
+                // Fast path: no per-row scale needed.  Every score of the chunk is at most
+                // max(raw accumulator) * (largest scale of the tile), or 0 when that maximum is
+                // not positive; fmaxf drops NaN.  One FMNMX tree, one multiply, one vote.
                 float mx[4];
 #pragma unroll
-                for (int g = 0; g < 4; ++g) mx[g] = fmaxf(fmaxf(s[4 * g], s[4 * g + 1]), fmaxf(s[4 * g + 2], s[4 * g + 3]));
-                // level 1: one vote for the whole chunk (the common case is "nothing to do")
-                if (!__any_sync(FULL, fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) >= thr)) return;
+                for (int g = 0; g < 4; ++g)
+                    mx[g] = fmaxf(fmaxf(__uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1])),
+                                  fmaxf(__uint_as_float(v[4 * g + 2]), __uint_as_float(v[4 * g + 3])));
+                const float mxc = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+                if (!__any_sync(FULL, fmaxf(mxc * smax, 0.f) >= thr)) return;
                 const long long cs = (dbg & 4) ? clock64() : 0;
-                // level 2 (warp-uniform entry): per group of 4, append the survivors
+                // Slow path (warp-uniform entry): exact scores with the per-row scales
+                float sc[16], s[16];
+                load_scale(sc, c);
+#pragma unroll
+                for (int j = 0; j < 16; ++j) s[j] = __uint_as_float(v[j]) * sc[j];
 #pragma unroll
                 for (int g = 0; g < 4; ++g) {
-                    if (__any_sync(FULL, mx[g] >= thr)) {
+                    const float mg = fmaxf(fmaxf(s[4 * g], s[4 * g + 1]), fmaxf(s[4 * g + 2], s[4 * g + 3]));
+                    if (__any_sync(FULL, mg >= thr)) {
                         if (dbg & 4) ++n_slow;
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
@@ -418,31 +444,21 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                     }
                 }
             };
-            auto load_scale = [&](float (&sc)[16], const int c) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const float4 f = *reinterpret_cast<const float4*>(scb + c + 4 * j);   // broadcast LDS.128
-                    sc[4 * j] = f.x; sc[4 * j + 1] = f.y; sc[4 * j + 2] = f.z; sc[4 * j + 3] = f.w;
-                }
-            };
             // Software pipeline over the set's 128 columns: the TMEM load of the next chunk is in
             // flight while the current one is processed (two register buffers, ping-pong).
             const long long cl = (dbg & 4) ? clock64() : 0;
             if (!(dbg & 1)) {
                 uint32_t va[16], vb[16];
-                float sa[16], sb[16];
                 const int c_lo = set * CPS, c_hi = (set + 1) * CPS;
                 tmem_ld16_issue(taddr0 + c_lo, va);
-                load_scale(sa, c_lo);
 #pragma unroll 1
                 for (int c = c_lo; c < c_hi; c += 32) {
                     tmem_ld_wait(va);
                     tmem_ld16_issue(taddr0 + c + 16, vb);
-                    load_scale(sb, c + 16);
-                    if (!(dbg & 2)) process(va, sa, c);
+                    if (!(dbg & 2)) process(va, c);
                     tmem_ld_wait(vb);
-                    if (c + 32 < c_hi) { tmem_ld16_issue(taddr0 + c + 32, va); load_scale(sa, c + 32); }
-                    if (!(dbg & 2)) process(vb, sb, c + 16);
+                    if (c + 32 < c_hi) tmem_ld16_issue(taddr0 + c + 32, va);
+                    if (!(dbg & 2)) process(vb, c + 16);
                 }
             }
             if (dbg & 4) t_loop += clock64() - cl;
@@ -455,10 +471,22 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                 mbar_arrive(bar_scempty + 8 * (int)(ti % SC_RING));     // scale slot may be refilled
             }
             if (++as == ACC_STAGES) { as = 0; aphase ^= 1; }
+            // Idle-time pruning: if the next accumulator is not ready yet, shrink the rows that are
+            // filling up now, off the critical path, so that prunes inside the column loop (which
+            // hold the accumulator stage and stall the MMA issuer) become rare.
+            if (!(dbg & 32) && t + 1 < t_hi && !mbar_test(bar_tfull + 8 * as, aphase)) {
+                const unsigned early = __ballot_sync(FULL, cnt > KPT + 8);
+                if (early) {
+                    const long long cp = (dbg & 4) ? clock64() : 0;
+                    warp_prune_rows<CAPT, KPT>(early, rows, lane, cnt, conv, thr, head32, cap32);
+                    if (((early >> lane) & 1u) && has_q) atomicMax(gthr + qrow, f2ord(thr));
+                    if (dbg & 4) { n_early += __popc(early); t_early += clock64() - cp; }
+                }
+            }
         }
         if ((dbg & 4) && lane == 0 && (blockIdx.x == 0 || blockIdx.x == 70) && (warp == 4 || warp == 9))
-            printf("[epi cta %d warp %d] total %lld cyc, wait accumulator-full %lld, column loop %lld (slow path %lld in %d groups, prune %lld for %d rows)\n",
-                   (int)blockIdx.x, warp, clock64() - t_start, w_tfull, t_loop, t_slow, n_slow, t_prune, n_prune);
+            printf("[epi cta %d warp %d] total %lld cyc, wait accumulator-full %lld, column loop %lld (slow path %lld in %d groups, prune %lld for %d rows), idle-time prune %lld for %d rows\n",
+                   (int)blockIdx.x, warp, clock64() - t_start, w_tfull, t_loop, t_slow, n_slow, t_prune, n_prune, t_early, n_early);
         // flush: final prune of every row, write this (slot, set) candidate list
         __syncwarp();
         for (int r = 0; r < 32; ++r) {
@@ -517,7 +545,7 @@ static cudaError_t launch_one(const ScanArgs& a, const CUtensorMap* map_q, const
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, scan_tc_kernel<CG, KPT>, *map_q, *map_c, a.scale, a.partials, a.gthr,
+    return cudaLaunchKernelEx(&cfg, scan_tc_kernel<CG, KPT>, *map_q, *map_c, a.scale, a.tile_max, a.partials, a.gthr,
                               a.nq, a.nslots, a.capacity, a.head, kblocks, a.slots, a.slots_rem, groups, a.dbg);
 }
 

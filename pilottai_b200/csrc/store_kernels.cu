@@ -76,14 +76,19 @@ convert_queries_kernel(const float* __restrict__ q, int64_t nq, int dim, int ld,
 // Per-search pre-pass: scale[n] = inverse norm of a candidate row, NaN for rows the
 // filter rejects (enhanced_memory.py:118-131 priority/tag filter, :20-21 expiry) and for
 // slots past the end.  NaN makes `score >= threshold` false in the scan for free.
+// One block = one 256-row tile per iteration; tile_max[t] = largest valid scale of tile t
+// (-inf when the whole tile is filtered): the scan's fast path bounds a whole chunk of
+// scores with it and only loads per-row scales on the rare hit.
 __global__ void __launch_bounds__(256)
 scale_kernel(const float* __restrict__ inv_norm, const int32_t* __restrict__ prio,
              const uint64_t* __restrict__ tagmask, const int64_t* __restrict__ expires,
              int64_t nslots, int64_t cap_pad, int32_t min_prio, uint64_t req, int64_t now_us,
-             float* __restrict__ scale) {
+             float* __restrict__ scale, float* __restrict__ tile_max) {
+    __shared__ float s_w[8];
     const float qnan = __int_as_float(0x7fc00000);
-    for (int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; n < cap_pad;
-         n += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t ntiles = cap_pad / 256;
+    for (int64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        const int64_t n = t * 256 + threadIdx.x;
         float s = qnan;
         if (n < nslots) {
             const int64_t e = expires[n];
@@ -91,6 +96,18 @@ scale_kernel(const float* __restrict__ inv_norm, const int32_t* __restrict__ pri
             if (ok) s = inv_norm[n];
         }
         scale[n] = s;
+        float m = fmaxf(-INFINITY, s);                    // fmaxf ignores NaN
+#pragma unroll
+        for (int j = 16; j > 0; j >>= 1) m = fmaxf(m, __shfl_xor_sync(FULL, m, j));
+        if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = m;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float mm = s_w[0];
+#pragma unroll
+            for (int w = 1; w < 8; ++w) mm = fmaxf(mm, s_w[w]);
+            tile_max[t] = mm;
+        }
+        __syncthreads();
     }
 }
 
@@ -156,9 +173,9 @@ cudaError_t launch_convert_queries(const float* q, int64_t nq, int dim, int ld, 
 
 cudaError_t launch_scale(const float* inv_norm, const int32_t* prio, const uint64_t* tagmask,
                          const int64_t* expires, int64_t nslots, int64_t cap_pad, int32_t min_prio,
-                         uint64_t req, int64_t now_us, float* scale, cudaStream_t st) {
+                         uint64_t req, int64_t now_us, float* scale, float* tile_max, cudaStream_t st) {
     scale_kernel<<<grid_for(cap_pad, 256, 148 * 8), 256, 0, st>>>(
-        inv_norm, prio, tagmask, expires, nslots, cap_pad, min_prio, req, now_us, scale);
+        inv_norm, prio, tagmask, expires, nslots, cap_pad, min_prio, req, now_us, scale, tile_max);
     return cudaGetLastError();
 }
 
