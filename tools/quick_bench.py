@@ -11,7 +11,7 @@ dim = int(sys.argv[2]) if len(sys.argv) > 2 else 768
 nq = int(sys.argv[3]) if len(sys.argv) > 3 else 1024
 iters = int(sys.argv[4]) if len(sys.argv) > 4 else 10
 kernels = sys.argv[5].split(",") if len(sys.argv) > 5 else ["generic", "tc", "tc_pair"]
-k = 10
+k = int(sys.argv[6]) if len(sys.argv) > 6 else 10
 torch.cuda.init()
 dev = torch.device("cuda:0")
 g = torch.Generator(device=dev); g.manual_seed(1234)
