@@ -230,7 +230,11 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
         if (cg == 1) map_c = h->map_c;
         else { rc = encode_map(&map_c, h->vec, h->capacity, h->ld, 128); if (rc) return rc; }
         a.slots = pilott::scan_tc_slots(nq, h->count, cg, ctas, &a.slots_rem);
-        a.list_len = ((h->opt_list_len == 16 && k <= 16) || (h->opt_list_len == 0 && k <= 12)) ? 16 : 32;
+        // 16-entry lists are enough whenever the lists together hold several times k candidates (the
+        // gap check in finish_kernel catches the rare query whose top-k crowd into one list).
+        const int nlists = (a.slots + (a.slots_rem > 0 ? 1 : 0)) * pilott::scan_tc_lists_per_slot();
+        const bool lists16 = k <= 12 || nlists >= 8;
+        a.list_len = (h->opt_list_len == 16 || (h->opt_list_len == 0 && lists16)) ? 16 : 32;
         lists = (a.slots + (a.slots_rem > 0 ? 1 : 0)) * pilott::scan_tc_lists_per_slot();
         f.rows_per_group = pilott::scan_tc_rows_per_group(cg);
         f.lists_base = a.slots * pilott::scan_tc_lists_per_slot();
@@ -262,7 +266,7 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
         if (e1) CK(cudaEventRecord(e1, st));
     }
     if (out_inexact) CK(cudaMemsetAsync(out_inexact, 0, 4, st));
-    f.partials = a.partials; f.slots = lists; f.list_len = a.list_len; f.qb = h->qbuf.p; f.vec = h->vec; f.ld = h->ld;
+    f.partials = a.partials; f.slots = lists; f.list_len = a.list_len; f.pool_n = k <= 12 ? 16 : 32; f.qb = h->qbuf.p; f.vec = h->vec; f.ld = h->ld;
     f.nq = nq; f.capacity = h->capacity; f.head = h->head; f.base_seq = h->total - h->count;
     f.k = k; f.seq_mul = h->seq_mul; f.seq_add = h->seq_add;
     f.err = h->ld * 2.4e-7 > 1e-4 ? h->ld * 2.4e-7 : 1e-4;

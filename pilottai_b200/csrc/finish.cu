@@ -112,7 +112,7 @@ constexpr int FIN_MAXLOADS = 8;   // 32-entry loads each warp prefetches at once
 // parallel (all their loads issued up front), warp 0 merges the four pools, re-scores the
 // survivors exactly and writes the result.
 __global__ void __launch_bounds__(FIN_WARPS * 32)
-finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_len, int rows_per_group,
+finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_len, int pool_n, int rows_per_group,
               int lists_base, int groups_rem, int lists_extra,
               const __nv_bfloat16* __restrict__ qb,
               const __nv_bfloat16* __restrict__ vec, int ld, int64_t nq, int64_t capacity,
@@ -171,8 +171,7 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_l
             if (s_bound[w] > bound) bound = s_bound[w];
         }
     }
-    // The pool that gets re-scored is as large as one candidate list (16 when k <= 12, else 32).
-    const int pool_n = list_len;
+    // pool_n = how many survivors get re-scored (16 when k <= 12, else 32).
     if (lane >= pool_n) best = 0ull;
     const size_t row_bytes = (size_t)ld * 2 + 16;           // +16: rows start on different bank groups
     if (stage_rows) {
@@ -240,15 +239,15 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_l
 
 cudaError_t launch_finish(const FinishArgs& a, cudaStream_t st) {
     if (a.nq <= 0) return cudaSuccess;
-    // stage the surviving rows in shared memory when they fit (list_len + 1 rows of ld*2+16 bytes)
-    const size_t smem = (size_t)(a.list_len + 1) * ((size_t)a.ld * 2 + 16);
+    // stage the surviving rows in shared memory when they fit (pool_n + 1 rows of ld*2+16 bytes)
+    const size_t smem = (size_t)(a.pool_n + 1) * ((size_t)a.ld * 2 + 16);
     const int stage_rows = smem <= 100 * 1024 ? 1 : 0;
     if (stage_rows) {
         cudaError_t e = cudaFuncSetAttribute(finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
     finish_kernel<<<(unsigned)a.nq, FIN_WARPS * 32, stage_rows ? smem : 0, st>>>(
-        a.partials, a.slots, a.list_len, a.rows_per_group, a.lists_base, a.groups_rem, a.lists_extra,
+        a.partials, a.slots, a.list_len, a.pool_n, a.rows_per_group, a.lists_base, a.groups_rem, a.lists_extra,
         (const __nv_bfloat16*)a.qb, (const __nv_bfloat16*)a.vec, a.ld, a.nq,
         a.capacity, a.head, a.base_seq, a.seq_mul, a.seq_add, a.k, a.err, a.out_idx, a.out_score, a.out_score64,
         a.flags, a.inexact, stage_rows);
