@@ -181,7 +181,8 @@ int pilott_topk_merge(const int64_t* idx_dev, const double* score64_dev, int n_s
  * words:            64-bit words per capability / specialization bit set (vocab <= 64*words)
  * task_req [nt,words]   required capabilities          task_tags [nt,words] task tags
  * task_type [nt]        specialization id of task.get('type','') (-1 = not in the vocabulary)
- * task_flags [nt]       bit0: 'required_capabilities' key present, bit1: 'type' key present
+ * task_flags [nt]       bit0: 'required_capabilities' key present, bit1: 'type' key present,
+ *                       bit2: some required capability is outside the vocabulary (no agent has it)
  * agent_caps/agent_spec [na,words]; agent_flags [na]: bit0 viable, bit1 has required-caps
  *                       attribute, bit2 has specializations
  * agent_s12 [na,3]      first two score terms for base in {missing-cap, no type match, type match}

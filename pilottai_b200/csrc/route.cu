@@ -48,7 +48,7 @@ route_kernel(const uint64_t* __restrict__ task_req, const uint64_t* __restrict__
             for (int w = 0; w < (W > 0 ? W : 1); ++w) { req[w] = task_req[t * nw + w]; tags[w] = task_tags[t * nw + w]; }
         }
     }
-    const bool has_req_key = tf & 1, has_type_key = tf & 2;
+    const bool has_req_key = tf & 1, has_type_key = tf & 2, req_unknown = tf & 4;
     double best = 0.0;
     int best_a = -1;
 
@@ -88,7 +88,7 @@ route_kernel(const uint64_t* __restrict__ task_req, const uint64_t* __restrict__
                 if (type >= 0) tbit = (s_spec[a * nw + (type >> 6)] >> (type & 63)) & 1;
             }
             // agent.py:551-556: key present and (attribute missing -> exception -> 0.0, or caps missing)
-            const bool zero_base = has_req_key && (!(f & 2) || missing);
+            const bool zero_base = has_req_key && (!(f & 2) || missing || req_unknown);
             const int sel = zero_base ? 0 : ((has_type_key && tbit) ? 2 : 1);   // agent.py:562-564
             double sc = s_s12[a * 3 + sel];
             if (mode == 0) {
@@ -117,8 +117,9 @@ cudaError_t launch_route(const uint64_t* task_req, const uint64_t* task_tags,
     const size_t fixed = 2 * (size_t)(max_tags + 1) * 8 + 64;
     int chunk = (int)((96 * 1024 - fixed) / per_agent);
     chunk &= ~7;                                   // keeps the uint64 sub-arrays 8-byte aligned
+    if (chunk < 8) return cudaErrorInvalidValue;            // vocabulary too wide for shared memory
     if (chunk > ((na + 7) & ~7)) chunk = (na + 7) & ~7;
-    if (chunk < 8) return cudaErrorInvalidValue;
+    if (chunk < 8) chunk = 8;                               // na == 0: every task gets "no agent"
     const size_t smem = fixed + (size_t)chunk * per_agent;
     const unsigned grid = (unsigned)((nt + 255) / 256);
 #define ROUTE_LAUNCH(WT)                                                                         \

@@ -136,17 +136,17 @@ def task_priority_host(task: dict) -> int:
 
 # ---- vocabularies and encoding -----------------------------------------------------------------
 class Vocab:
-    """String -> bit position.  Capability bit 0 is reserved for 'a capability no agent has'."""
+    """String -> bit position.  A required capability no agent has is carried as task flag bit 2."""
 
     def __init__(self, agents: Sequence[dict]):
         self.cap: Dict[str, int] = {}
         self.spec: Dict[str, int] = {}
         for a in agents:
             for c in a.get("caps") or ():
-                self.cap.setdefault(c, len(self.cap) + 1)
+                self.cap.setdefault(c, len(self.cap))
             for s in a.get("specializations") or ():
                 self.spec.setdefault(s, len(self.spec))
-        self.words = max(1, (len(self.cap) + 1 + 63) // 64, (len(self.spec) + 63) // 64)
+        self.words = max(1, (len(self.cap) + 63) // 64, (len(self.spec) + 63) // 64)
 
     def _mask(self, bits: Iterable[int]) -> np.ndarray:
         out = np.zeros(self.words, dtype=np.uint64)
@@ -161,7 +161,7 @@ class Vocab:
         return self._mask(self.spec[s] for s in specs or ())
 
     def req_mask(self, required) -> np.ndarray:
-        return self._mask(self.cap.get(c, 0) for c in set(required))       # unknown capability -> bit 0
+        return self._mask(self.cap[c] for c in set(required) if c in self.cap)
 
     def tag_mask(self, tags) -> np.ndarray:
         return self._mask(self.spec[t] for t in set(tags) if t in self.spec)
@@ -177,6 +177,8 @@ def encode_tasks(tasks: Sequence[dict], vocab: Vocab) -> Dict[str, np.ndarray]:
         if "required_capabilities" in t:
             flags[i] |= 1
             req[i] = vocab.req_mask(t["required_capabilities"])
+            if any(c not in vocab.cap for c in t["required_capabilities"]):
+                flags[i] |= 4                      # a capability nobody has: every agent misses it
         if "type" in t:
             flags[i] |= 2
         typ[i] = vocab.spec.get(t.get("type", ""), -1)
@@ -236,7 +238,11 @@ class RoutingEngine:
                 ok = False
             s12[i], t4[i] = s, t
             flags[i] |= 1 if ok else 0
-        tab = (self._d(s12), self._d(t4), self._d(flags))
+        # Only viable agents can win, so only they go to the device (table order is kept: the
+        # first maximum among viable agents is the first maximum overall).
+        keep = np.nonzero(flags & 1)[0].astype(np.int64)
+        tab = (self._d(s12[keep]), self._d(t4[keep]), self._d(flags[keep]), self.d_caps[keep] if keep.size else self.d_caps[:0],
+               self.d_spec[keep] if keep.size else self.d_spec[:0], self._torch.from_numpy(keep.astype(np.int32)).to(self.device))
         self._tables[key] = tab
         return tab
 
@@ -244,16 +250,18 @@ class RoutingEngine:
         """enc: arrays from encode_tasks (numpy) or the same keys as CUDA tensors.
         Returns (agent index int32 [T] (-1 = none), score fp64 [T]) as CUDA tensors."""
         torch = self._torch
-        d_s12, d_t4, d_flags = self._table(mode, **cfg)
+        d_s12, d_t4, d_flags, d_caps, d_spec, d_keep = self._table(mode, **cfg)
         t = {k: (self._d(v) if isinstance(v, np.ndarray) else v) for k, v in enc.items()}
         nt = t["type"].shape[0]
         out_a = torch.empty(nt, dtype=torch.int32, device=self.device)
         out_s = torch.empty(nt, dtype=torch.float64, device=self.device)
         st = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
         check(self._lib.pilott_route_score(ptr(t["req"]), ptr(t["tags"]), ptr(t["type"]), ptr(t["flags"]), nt,
-                                           ptr(self.d_caps), ptr(self.d_spec), ptr(d_flags), ptr(d_s12), ptr(d_t4),
-                                           len(self.agents), self.vocab.words, ptr(self.d_u), self.max_tags,
+                                           ptr(d_caps), ptr(d_spec), ptr(d_flags), ptr(d_s12), ptr(d_t4),
+                                           int(d_keep.numel()), self.vocab.words, ptr(self.d_u), self.max_tags,
                                            MODE[mode], ptr(out_a), ptr(out_s), st))
+        if 0 < d_keep.numel() < len(self.agents):      # map compacted positions back to table indices
+            out_a = torch.where(out_a >= 0, d_keep[out_a.clamp(min=0).long()], out_a)
         return out_a, out_s
 
     def route(self, tasks: Sequence[dict], mode: str = "router", **cfg):

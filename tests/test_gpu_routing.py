@@ -94,7 +94,7 @@ def test_router_wide_vocabulary_generic_words(torch_cuda):
     for t in tasks[::3]:
         t["required_capabilities"] = [str(c) for c in rng.choice(big, 2, replace=False)]
     eng = RoutingEngine(agents, 0)
-    assert eng.vocab.words == 4
+    assert eng.vocab.words == 4          # 64 + 150 capabilities -> 214 bits
     idx, sc = eng.route(tasks, "router", load_threshold=0.8)
     for t, i, s in zip(tasks, idx, sc):
         want, ws = ro.router_route(agents, t, 0.8)

@@ -26,7 +26,7 @@ def emulate_kernel(enc, caps, spec, attr_flags, s12, t4, viable, u, max_tags, mo
             missing = bool(np.any(enc["req"][t] & ~caps[a]))
             tagc = int(sum(bin(int(x)).count("1") for x in (enc["tags"][t] & spec[a])))
             tbit = ty >= 0 and bool((int(spec[a][ty >> 6]) >> (ty & 63)) & 1)
-            zero = has_req and (not (attr_flags[a] & 2) or missing)
+            zero = has_req and (not (attr_flags[a] & 2) or missing or bool(enc["flags"][t] & 4))
             sel = 0 if zero else (2 if (has_type and tbit) else 1)
             sc = float(s12[a][sel])
             if mode == 0:
@@ -113,9 +113,11 @@ def test_delegator_host_terms_match_reference(golden_dir, name):
             assert float(s).hex() == r["score"]
 
 
-def test_vocab_reserves_unknown_capability_bit():
+def test_vocab_and_unknown_capability_flag():
     agents = [{"caps": ["a", "b"], "specializations": ["x"]}, {"caps": None, "specializations": None}]
     v = R.Vocab(agents)
-    assert v.cap == {"a": 1, "b": 2} and v.spec == {"x": 0} and v.words == 1
-    assert int(v.req_mask(["a", "zzz"])[0]) == 0b011          # unknown -> bit 0, which no agent owns
+    assert v.cap == {"a": 0, "b": 1} and v.spec == {"x": 0} and v.words == 1
+    assert int(v.req_mask(["a", "zzz"])[0]) == 0b01           # unknown capability: not a bit ...
+    enc = R.encode_tasks([{"required_capabilities": ["a", "zzz"]}, {"required_capabilities": ["a"]}, {}], v)
+    assert list(enc["flags"]) == [1 | 4, 1, 0]                # ... but task flag bit 2
     assert int(v.tag_mask(["x", "x", "nope"])[0]) == 1
