@@ -266,7 +266,8 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
         if (e1) CK(cudaEventRecord(e1, st));
     }
     if (out_inexact) CK(cudaMemsetAsync(out_inexact, 0, 4, st));
-    f.partials = a.partials; f.slots = lists; f.list_len = a.list_len; f.pool_n = k <= 12 ? 16 : 32; f.qb = h->qbuf.p; f.vec = h->vec; f.ld = h->ld;
+    f.partials = a.partials; f.slots = lists; f.list_len = a.list_len; f.qb = h->qbuf.p; f.vec = h->vec; f.ld = h->ld;
+    f.pool_n = 32;   // always re-score 32 survivors: a wide margin below the k-th keeps the gap check quiet at 10M+ rows
     f.nq = nq; f.capacity = h->capacity; f.head = h->head; f.base_seq = h->total - h->count;
     f.k = k; f.seq_mul = h->seq_mul; f.seq_add = h->seq_add;
     f.err = h->ld * 2.4e-7 > 1e-4 ? h->ld * 2.4e-7 : 1e-4;

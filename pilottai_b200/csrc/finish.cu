@@ -171,7 +171,7 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_l
             if (s_bound[w] > bound) bound = s_bound[w];
         }
     }
-    // pool_n = how many survivors get re-scored (16 when k <= 12, else 32).
+    // pool_n = how many survivors get re-scored.
     if (lane >= pool_n) best = 0ull;
     const size_t row_bytes = (size_t)ld * 2 + 16;           // +16: rows start on different bank groups
     if (stage_rows) {

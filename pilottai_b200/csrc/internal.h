@@ -48,7 +48,7 @@ cudaError_t launch_scale(const float* inv_norm, const int32_t* prio, const uint6
 
 struct FinishArgs {
     const uint64_t* partials; int slots; int list_len;   // slots = allocated lists per query
-    int pool_n;                 // survivors re-scored exactly: 16 or 32 (>= k)
+    int pool_n;                 // survivors re-scored exactly (32)
     int rows_per_group, lists_base, groups_rem, lists_extra;  // lists of query q: lists_base + (q/rows_per_group < groups_rem ? lists_extra : 0)
     const void* qb; const void* vec; int ld;
     int64_t nq, capacity, head, base_seq;
