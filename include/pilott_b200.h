@@ -165,6 +165,12 @@ int pilott_topk_merge(const int64_t* idx_dev, const double* score64_dev, int n_s
                       int k, int64_t* out_idx_dev, float* out_score_dev, double* out_score64_dev,
                       void* stream);
 
+/* Same merge for ONE gathered buffer: packed is [n_shards][2][nq][k] 64-bit words, plane 0 the
+ * int64 indices and plane 1 the fp64 scores of a shard -- what a single all-gather of each
+ * rank's (index, score) block produces. */
+int pilott_topk_merge_packed(const int64_t* packed_dev, int n_shards, int64_t nq, int k,
+                             int64_t* out_idx_dev, float* out_score_dev, double* out_score64_dev, void* stream);
+
 /* ---- routing -----------------------------------------------------------------------
  * One call scores nt tasks against na agents and returns, per task, the first agent with
  * the maximal score among the viable ones (-1 = none) -- the inner loops of

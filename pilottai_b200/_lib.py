@@ -44,6 +44,7 @@ SIGNATURES = {
     "pilott_mem_compact": (C.c_int, [c_vp, c_i64, C.POINTER(c_i64), c_vp]),
     "pilott_mem_export": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "pilott_topk_merge": (C.c_int, [c_vp, c_vp, C.c_int, c_i64, C.c_int, c_vp, c_vp, c_vp, c_vp]),
+    "pilott_topk_merge_packed": (C.c_int, [c_vp, C.c_int, c_i64, C.c_int, c_vp, c_vp, c_vp, c_vp]),
     "pilott_route_score": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, C.c_int,
                                      C.c_int, c_vp, C.c_int, C.c_int, c_vp, c_vp, c_vp]),
     "pilott_task_priority": (C.c_int, [c_vp, c_vp, c_vp, c_i64, c_vp, c_vp]),

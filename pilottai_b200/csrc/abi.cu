@@ -657,8 +657,18 @@ int pilott_topk_merge(const int64_t* idx_dev, const double* score64_dev, int n_s
     if (nq < 0 || n_shards < 1 || k < 1) return fail(PILOTT_EINVAL, "bad merge shape");
     if ((int64_t)n_shards * k > 2048) return fail(PILOTT_EINVAL, "n_shards * k must be <= 2048");
     if (nq > 0 && (!idx_dev || !score64_dev || !out_idx_dev || !out_score_dev)) return fail(PILOTT_EINVAL, "NULL pointer");
-    CK(pilott::launch_topk_merge(idx_dev, score64_dev, n_shards, nq, k, out_idx_dev, out_score_dev,
+    CK(pilott::launch_topk_merge(idx_dev, score64_dev, n_shards, nq, k, nq * k, out_idx_dev, out_score_dev,
                                  out_score64_dev, (cudaStream_t)stream));
+    return PILOTT_OK;
+}
+
+int pilott_topk_merge_packed(const int64_t* packed_dev, int n_shards, int64_t nq, int k,
+                             int64_t* out_idx_dev, float* out_score_dev, double* out_score64_dev, void* stream) {
+    if (nq < 0 || n_shards < 1 || k < 1) return fail(PILOTT_EINVAL, "bad merge shape");
+    if ((int64_t)n_shards * k > 2048) return fail(PILOTT_EINVAL, "n_shards * k must be <= 2048");
+    if (nq > 0 && (!packed_dev || !out_idx_dev || !out_score_dev)) return fail(PILOTT_EINVAL, "NULL pointer");
+    CK(pilott::launch_topk_merge(packed_dev, reinterpret_cast<const double*>(packed_dev + nq * k), n_shards, nq, k,
+                                 2 * nq * k, out_idx_dev, out_score_dev, out_score64_dev, (cudaStream_t)stream));
     return PILOTT_OK;
 }
 

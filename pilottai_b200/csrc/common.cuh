@@ -105,6 +105,69 @@ __device__ __forceinline__ uint64_t warp_prune(uint64_t* buf, int cnt, int conv,
 
 // Prune every row of this warp's 32-row group whose bit is set in `mask`.
 // rows = base of the warp's 32 row buffers (row r at rows + r*CAPT).
+// B independent bitonic sorts, step loop outermost so the B dependency chains interleave.
+template <bool DESC, int B>
+__device__ __forceinline__ void warp_sort64_multi(uint64_t (&v)[B], int lane) {
+#pragma unroll
+    for (int k = 2; k <= 32; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            const bool up = (((lane & k) == 0) != DESC);
+            const bool keep_min = (((lane & j) == 0) == up);
+#pragma unroll
+            for (int i = 0; i < B; ++i) {
+                const uint64_t o = shfl_xor64(v[i], j);
+                const uint64_t mn = v[i] < o ? v[i] : o, mx = v[i] < o ? o : v[i];
+                v[i] = keep_min ? mn : mx;
+            }
+        }
+    }
+}
+
+// warp_prune for B rows at once (same results; ~B times the work in about the latency of one).
+template <int CAPT, int KPT, int B>
+__device__ __forceinline__ void warp_prune_multi(uint64_t* const (&buf)[B], const int (&cnt)[B], const int (&conv)[B],
+                                                 uint32_t head, uint32_t cap, int lane, uint64_t (&m)[B],
+                                                 int (&new_cnt)[B], float (&new_thr)[B]) {
+    uint64_t a[B], b[B];
+#pragma unroll
+    for (int i = 0; i < B; ++i) {
+        a[i] = lane < cnt[i] ? buf[i][lane] : 0ull;
+        b[i] = (CAPT > 32 && (lane + 32) < cnt[i]) ? buf[i][lane + 32] : 0ull;
+        if (lane < cnt[i] && lane >= conv[i]) a[i] = raw_to_key(a[i], head, cap);
+        if ((lane + 32) < cnt[i] && (lane + 32) >= conv[i]) b[i] = raw_to_key(b[i], head, cap);
+    }
+    warp_sort64_multi<true, B>(a, lane);
+    warp_sort64_multi<false, B>(b, lane);
+    uint64_t mn[B];
+#pragma unroll
+    for (int i = 0; i < B; ++i) {
+        m[i] = a[i] > b[i] ? a[i] : b[i];
+        if (KPT == 16) {
+            const uint64_t o = shfl_xor64(m[i], 16);
+            m[i] = (lane < 16) ? (m[i] > o ? m[i] : o) : 0ull;
+        }
+        mn[i] = m[i];
+    }
+#pragma unroll
+    for (int j = KPT / 2; j > 0; j >>= 1) {
+#pragma unroll
+        for (int i = 0; i < B; ++i) {
+            const uint64_t o = shfl_xor64(mn[i], j);
+            mn[i] = mn[i] < o ? mn[i] : o;
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < B; ++i) {
+        mn[i] = shfl64(mn[i], 0);
+        if (lane < KPT) buf[i][lane] = m[i];
+        new_cnt[i] = cnt[i] < KPT ? cnt[i] : KPT;
+        new_thr[i] = cnt[i] >= KPT ? key_score(mn[i]) : -INFINITY;
+    }
+}
+
+// Prune every row of this warp's 32-row group whose bit is set in `mask`.
+// rows = base of the warp's 32 row buffers (row r at rows + r*CAPT).
 template <int CAPT, int KPT>
 __device__ __forceinline__ void warp_prune_rows(unsigned mask, uint64_t* rows, int lane, int& cnt,
                                                 int& conv, float& thr, uint32_t head, uint32_t cap) {
@@ -118,6 +181,33 @@ __device__ __forceinline__ void warp_prune_rows(unsigned mask, uint64_t* rows, i
         float nt;
         warp_prune<CAPT, KPT>(rows + r * CAPT, c, cv, head, cap, lane, nc, nt);
         if (lane == r) { cnt = nc; conv = nc; thr = nt; }
+    }
+    __syncwarp();
+}
+
+// Prune ALL 32 rows, four at a time (the end-of-sweep flush, where every row needs it and the
+// MMA pipe is already idle: latency is all that matters).  Kept out of the hot loop on purpose:
+// inlining it there costs more in instruction-cache misses than it saves.
+template <int CAPT, int KPT>
+__device__ __forceinline__ void warp_prune_all_rows(uint64_t* rows, int lane, int& cnt, int& conv, float& thr,
+                                                    uint32_t head, uint32_t cap) {
+    __syncwarp();
+#pragma unroll 1
+    for (int r0 = 0; r0 < 32; r0 += 4) {
+        int c[4], cv[4], nc[4];
+        float nt[4];
+        uint64_t* bp[4];
+        uint64_t m[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            c[i] = __shfl_sync(FULL, cnt, r0 + i);
+            cv[i] = __shfl_sync(FULL, conv, r0 + i);
+            bp[i] = rows + (r0 + i) * CAPT;
+        }
+        warp_prune_multi<CAPT, KPT, 4>(bp, c, cv, head, cap, lane, m, nc, nt);
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            if (lane == r0 + i) { cnt = nc[i]; conv = nc[i]; thr = nt[i]; }
     }
     __syncwarp();
 }

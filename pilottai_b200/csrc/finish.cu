@@ -358,7 +358,7 @@ cudaError_t launch_exact(const void* qb, const void* vec, int ld, const int32_t*
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 topk_merge_kernel(const int64_t* __restrict__ idx, const double* __restrict__ sc, int shards, int64_t nq,
-                  int k, int64_t* __restrict__ out_idx, float* __restrict__ out_score,
+                  int k, int64_t shard_stride, int64_t* __restrict__ out_idx, float* __restrict__ out_score,
                   double* __restrict__ out_score64) {
     extern __shared__ __align__(16) unsigned char sm_raw[];
     const int total = shards * k;
@@ -367,8 +367,8 @@ topk_merge_kernel(const int64_t* __restrict__ idx, const double* __restrict__ sc
     const int64_t q = blockIdx.x;
     for (int i = threadIdx.x; i < total; i += blockDim.x) {
         const int sh = i / k, j = i % k;
-        s_sc[i] = sc[((int64_t)sh * nq + q) * k + j];
-        s_idx[i] = idx[((int64_t)sh * nq + q) * k + j];
+        s_sc[i] = sc[(int64_t)sh * shard_stride + q * k + j];
+        s_idx[i] = idx[(int64_t)sh * shard_stride + q * k + j];
     }
     for (int j = threadIdx.x; j < k; j += blockDim.x) {
         out_idx[q * k + j] = -1;
@@ -392,11 +392,11 @@ topk_merge_kernel(const int64_t* __restrict__ idx, const double* __restrict__ sc
 }
 
 cudaError_t launch_topk_merge(const int64_t* idx, const double* sc, int shards, int64_t nq, int k,
-                              int64_t* out_idx, float* out_score, double* out_score64,
-                              cudaStream_t st) {
+                              int64_t shard_stride, int64_t* out_idx, float* out_score,
+                              double* out_score64, cudaStream_t st) {
     if (nq <= 0) return cudaSuccess;
     const size_t smem = (size_t)shards * k * 16;
-    topk_merge_kernel<<<(unsigned)nq, 256, smem, st>>>(idx, sc, shards, nq, k, out_idx, out_score,
+    topk_merge_kernel<<<(unsigned)nq, 256, smem, st>>>(idx, sc, shards, nq, k, shard_stride, out_idx, out_score,
                                                        out_score64);
     return cudaGetLastError();
 }

@@ -68,8 +68,8 @@ cudaError_t launch_exact(const void* qb, const void* vec, int ld, const int32_t*
                          cudaStream_t st);
 
 cudaError_t launch_topk_merge(const int64_t* idx, const double* sc, int shards, int64_t nq, int k,
-                              int64_t* out_idx, float* out_score, double* out_score64,
-                              cudaStream_t st);
+                              int64_t shard_stride, int64_t* out_idx, float* out_score,
+                              double* out_score64, cudaStream_t st);
 
 cudaError_t launch_compact_flags(const int64_t* expires, int64_t count, int64_t head,
                                  int64_t capacity, int64_t now_us, uint8_t* keep, cudaStream_t st);

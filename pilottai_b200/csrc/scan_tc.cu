@@ -487,15 +487,13 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
         if ((dbg & 4) && lane == 0 && (blockIdx.x == 0 || blockIdx.x == 70) && (warp == 4 || warp == 9))
             printf("[epi cta %d warp %d] total %lld cyc, wait accumulator-full %lld, column loop %lld (slow path %lld in %d groups, prune %lld for %d rows), idle-time prune %lld for %d rows\n",
                    (int)blockIdx.x, warp, clock64() - t_start, w_tfull, t_loop, t_slow, n_slow, t_prune, n_prune, t_early, n_early);
-        // flush: final prune of every row, write this (slot, set) candidate list
-        __syncwarp();
+        // flush: final prune of every row (four at a time), write this (slot, set) candidate list
+        warp_prune_all_rows<CAPT, KPT>(rows, lane, cnt, conv, thr, head32, cap32);
         for (int r = 0; r < 32; ++r) {
             const int c = __shfl_sync(FULL, cnt, r);
-            const int cv = __shfl_sync(FULL, conv, r);
-            int nc; float nt;
-            const uint64_t m = warp_prune<CAPT, KPT>(rows + r * CAPT, c, cv, head32, cap32, lane, nc, nt);
             const int64_t q = q0 + quarter * 32 + r;
-            if (q < nq && lane < KPT) partials[(q * max_lists + slot * EPI_SETS + set) * KPT + lane] = m;
+            if (q < nq && lane < KPT)
+                partials[(q * max_lists + slot * EPI_SETS + set) * KPT + lane] = lane < c ? rows[r * CAPT + lane] : 0ull;
         }
     }
 

@@ -16,7 +16,7 @@ import numpy as np
 import torch
 import torch.distributed as dist
 
-from .store import SemanticStore, topk_merge
+from .store import SemanticStore, topk_merge_packed
 
 
 def shard_rows(first_global: int, n: int, rank: int, world: int) -> np.ndarray:
@@ -33,7 +33,7 @@ class ShardedSemanticStore:
         self.local.set_sequence_map(world, rank)
         self.dim, self.device = dim, device
         self.total = 0                                  # global rows ever appended
-        self._gi = self._gs = None
+        self._bufs = {}
 
     def append(self, x, prio=None, tagmask=None, expires_us=None) -> int:
         """Every rank calls this with the SAME global batch (host numpy or CUDA tensor); each
@@ -51,20 +51,42 @@ class ShardedSemanticStore:
         self.total += n
         return first
 
+    def _buffers(self, nq: int, k: int, dev, slot: int):
+        key = (nq, k, slot)
+        if key not in self._bufs:
+            mine = torch.empty((2, nq, k), dtype=torch.int64, device=dev)          # [0] indices, [1] fp64 score bits
+            self._bufs[key] = {
+                "mine": mine, "idx": mine[0], "sc64": mine[1].view(torch.float64),
+                "sc": torch.empty((nq, k), dtype=torch.float32, device=dev),
+                "flags": torch.empty(nq, dtype=torch.uint8, device=dev),
+                "inexact": torch.zeros(1, dtype=torch.int32, device=dev),
+                "gathered": torch.empty((self.world, 2, nq, k), dtype=torch.int64, device=dev),
+            }
+        return self._bufs[key]
+
+    def search_begin(self, q: torch.Tensor, k: int, slot: int = 0, **flt):
+        """Local search + ONE asynchronous all-gather of the packed (index, score) block.
+        Returns a ticket for search_end(); with two slots a caller overlaps the exchange of
+        batch i with the local search of batch i+1."""
+        b = self._buffers(q.shape[0], k, q.device, slot)
+        self.local.search_into(q, k, b["idx"], b["sc"], b["sc64"], b["inexact"], b["flags"], **flt)
+        work = None
+        if self.world > 1:
+            work = dist.all_gather_into_tensor(b["gathered"], b["mine"], group=self.group, async_op=True)
+        return b, work
+
+    def search_end(self, ticket):
+        b, work = ticket
+        if self.world == 1:
+            return b["idx"], b["sc"], b["sc64"], b["inexact"]
+        work.wait()
+        m_idx, m_sc, m_sc64 = topk_merge_packed(b["gathered"])
+        return m_idx, m_sc, m_sc64, b["inexact"]
+
     def search(self, q: torch.Tensor, k: int, **flt):
         """q: CUDA fp32 [Q, dim], same on every rank.  Returns (idx, score, score64) on every rank,
         plus the local inexact counter (callers check it, see SemanticStore.search)."""
-        idx, sc, sc64, inexact, flags = self.local.search(q, k, want_score64=True, **flt)
-        if self.world == 1:
-            return idx, sc, sc64, inexact
-        nq = q.shape[0]
-        if self._gi is None or self._gi.shape[1:] != (nq, k):
-            self._gi = torch.empty((self.world, nq, k), dtype=torch.int64, device=q.device)
-            self._gs = torch.empty((self.world, nq, k), dtype=torch.float64, device=q.device)
-        dist.all_gather_into_tensor(self._gi, idx, group=self.group)
-        dist.all_gather_into_tensor(self._gs, sc64, group=self.group)
-        m_idx, m_sc, m_sc64 = topk_merge(self._gi, self._gs)
-        return m_idx, m_sc, m_sc64, inexact
+        return self.search_end(self.search_begin(q, k, 0, **flt))
 
     def close(self):
         self.local.close()

@@ -252,3 +252,18 @@ def topk_merge(idx, score64, k: Optional[int] = None):
     st = C.c_void_p(torch.cuda.current_stream(idx.device).cuda_stream)
     check(lib.pilott_topk_merge(ptr(idx), ptr(score64), shards, nq, k, ptr(o_idx), ptr(o_sc), ptr(o_sc64), st))
     return o_idx, o_sc, o_sc64
+
+
+def topk_merge_packed(packed, out=None):
+    """[shards, 2, nq, k] int64 words (plane 0 indices, plane 1 fp64 score bits) -> global top-k."""
+    torch = _torch()
+    lib = _lib.load()
+    shards, two, nq, k = packed.shape
+    assert two == 2 and packed.dtype == torch.int64 and packed.is_contiguous()
+    if out is None:
+        out = (torch.empty((nq, k), dtype=torch.int64, device=packed.device),
+               torch.empty((nq, k), dtype=torch.float32, device=packed.device),
+               torch.empty((nq, k), dtype=torch.float64, device=packed.device))
+    st = C.c_void_p(torch.cuda.current_stream(packed.device).cuda_stream)
+    check(lib.pilott_topk_merge_packed(ptr(packed), shards, nq, k, ptr(out[0]), ptr(out[1]), ptr(out[2]), st))
+    return out
