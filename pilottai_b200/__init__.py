@@ -5,6 +5,8 @@ Host-side mirrors of the reference API (import these instead of the `pilott.*` o
     TaskRouter, RouterConfig, TaskPriority          (pilott/core/router.py)
     LoadBalancer, LoadBalancerConfig, LoadMetrics   (pilott/orchestration/load_balancer.py)
     TaskDelegator                                   (pilott/delegation/task_delegator.py)
+    KnowledgeManager, KnowledgeSource               (pilott/knowledge/knowledge_manager.py)
+`serve_adapter.attach(serve)` wires the router and the memory into a reference `Serve`.
 Lower level: SemanticStore (store.py), RoutingEngine (routing.py), ShardedSemanticStore
 (sharded.py).  Everything runs through libpilott_b200.so (include/pilott_b200.h); there is no
 CPU fallback.  Submodules are imported lazily so that `import pilottai_b200` works on a box
@@ -17,6 +19,7 @@ _LAZY = {
     "TaskRouter": "orchestration", "RouterConfig": "orchestration", "TaskPriority": "orchestration",
     "LoadBalancer": "orchestration", "LoadBalancerConfig": "orchestration", "LoadMetrics": "orchestration",
     "TaskDelegator": "orchestration",
+    "KnowledgeManager": "knowledge", "KnowledgeSource": "knowledge", "SemanticMemorySource": "knowledge",
     "SemanticStore": "store", "RoutingEngine": "routing", "ShardedSemanticStore": "sharded",
 }
 

@@ -166,3 +166,58 @@ def test_enhanced_memory_dropin_semantics(torch_cuda):
         assert (await mem.get_recent_tasks(task_type="a"))[0]["data"]["type"] == "a" and await mem.get_pattern("p") == 5
         mem.close()
     asyncio.run(scenario())
+
+
+def test_knowledge_manager_fronts_the_semantic_store(torch_cuda):
+    from pilottai_b200 import EnhancedMemory
+    from pilottai_b200.knowledge import KnowledgeManager, SemanticMemorySource
+
+    async def scenario():
+        mem = EnhancedMemory(max_size=200, dim=128)
+        for i in range(40):
+            await mem.store_semantic(f"note {i}: the {['red', 'green', 'blue'][i % 3]} widget ships in batch {i}",
+                                     metadata={"i": i}, priority=i % 3)
+        km = KnowledgeManager()
+        src = SemanticMemorySource(mem, limit=3)
+        assert await km.add_source(src) is True
+        r1 = await km.query_knowledge("note 17: the blue widget ships in batch 17", ["semantic_memory"])
+        assert r1[0][0]["metadata"]["i"] == 17 and len(r1[0]) == 3
+        launches = mem._store.launch_count()
+        r2 = await km.query_knowledge("note 17: the blue widget ships in batch 17", ["semantic_memory"])
+        assert r2 == r1 and mem._store.launch_count() == launches          # cache hit: no device work
+        assert km.get_source_stats()["semantic_memory"]["access_count"] == 1
+        mem.close()
+    asyncio.run(scenario())
+
+
+def test_serve_adapter_wires_router_and_memory(torch_cuda, golden_dir):
+    from pilottai_b200.serve_adapter import attach, task_to_dict
+    g = _load(golden_dir, "mid")
+    agents = {f"role{i}": FakeAgent(r) for i, r in enumerate(g["agents"])}
+
+    class FakeServe:                      # the attributes of pilott.Serve the adapter touches
+        def __init__(self):
+            self.agents, self.stored, self.logger = agents, [], types.SimpleNamespace(error=lambda *a: None)
+
+        async def _select_agent(self, task):            # reference default: first non-busy (pilott.py:494-496)
+            return next(a for a in self.agents.values() if a.status != "busy")
+
+        async def _update_memory(self, task, result):
+            self.stored.append(task)
+
+    async def scenario():
+        serve = FakeServe()
+        first_non_busy = await serve._select_agent(None)
+        router, mem = attach(serve, device=0)
+        picks = [await serve._select_agent(t) for t in g["tasks"][:25]]
+        assert [a.id for a in picks] == [r["agent"] for r in g["router"][:25]]       # routed, not first-non-busy
+        assert any(a.id != first_non_busy.id for a in picks)
+        task = types.SimpleNamespace(id="t-1", description="summarise the quarterly pdf report",
+                                     metadata={"type": "spec03", "tags": ["spec01"]}, complexity=9, dependencies=[])
+        assert task_to_dict(task)["type"] == "spec03" and task_to_dict(task)["complexity"] == 9
+        await serve._update_memory(task, types.SimpleNamespace(success=True))
+        assert serve.stored == [task] and len(mem) == 1
+        hit = await agents["role0"].enhanced_memory.semantic_search("quarterly pdf report summary", limit=1)
+        assert hit[0].metadata["task_id"] == "t-1" and hit[0].priority == 1
+        mem.close()
+    asyncio.run(scenario())
