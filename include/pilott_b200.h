@@ -59,7 +59,9 @@ int pilott_mem_info(const pilott_mem_t* h, int64_t* total, int64_t* count, int64
  * which = 3: candidates each partial list keeps: 0 auto (16 when k <= 12 or the scan produces >= 8 lists per query, else 32), 16, 32.
  * which = 4: 1 = record CUDA events around the scan kernel (read with pilott_mem_profile_read).
  * which = 5 / 6: reported index = sequence * stride (5) + offset (6); a row-sharded store that
- *            holds global rows i with i % world == rank uses stride = world, offset = rank. */
+ *            holds global rows i with i % world == rank uses stride = world, offset = rank.
+ * which = 7: set `total` (rows ever appended, >= rows held): a restored snapshot continues the
+ *            sequence numbering of the store it was taken from. */
 int pilott_mem_set_option(pilott_mem_t* h, int which, int64_t value);
 /* Kernel launches enqueued by this handle since creation (bench bookkeeping). */
 int64_t pilott_mem_launch_count(const pilott_mem_t* h);

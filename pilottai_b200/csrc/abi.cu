@@ -398,6 +398,9 @@ int pilott_mem_set_option(pilott_mem_t* h, int which, int64_t value) {
     } else if (which == 1) {
         if (value < 0 || value > 4096) return fail(PILOTT_EINVAL, "CTA count out of range");
         h->opt_ctas = (int)value;
+    } else if (which == 7) {
+        if (value < h->count) return fail(PILOTT_EINVAL, "total cannot be smaller than the rows held");
+        h->total = value;        // restoring a snapshot: continue the sequence numbering where it stopped
     } else if (which == 4) {
         h->profile = value != 0;
     } else if (which == 5) {

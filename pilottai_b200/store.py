@@ -238,6 +238,31 @@ class SemanticStore:
         return out
 
 
+def save_snapshot(store: "SemanticStore", path: str) -> None:
+    """Corpus snapshot (the reference has no persistence): the held rows in
+    age order -- bf16 bit patterns and metadata columns -- plus the ring bookkeeping."""
+    ex = store.export()
+    info = store.info()
+    np.savez(path, vec_bits=ex["vec_bits"], prio=ex["prio"], tagmask=ex["tagmask"], expires_us=ex["expires_us"],
+             meta=np.array([info["dim"], info["capacity"], info["total"]], dtype=np.int64))
+
+
+def load_snapshot(path: str, device: int = 0, capacity: Optional[int] = None) -> "SemanticStore":
+    """Rebuilds a store from save_snapshot().  bf16 -> fp32 is exact and fp32 -> bf16 (RNE) of an
+    exactly representable value gives the same bits back, so rows, inverse norms and therefore
+    every search result are bit-identical to the original store's."""
+    z = np.load(path if path.endswith(".npz") else path + ".npz")
+    dim, cap, total = (int(v) for v in z["meta"])
+    st = SemanticStore(dim, capacity or cap, device)
+    x = (z["vec_bits"].astype(np.uint32) << 16).view(np.float32)
+    step = max(1, min(st.capacity, 1 << 18))
+    for lo in range(0, x.shape[0], step):
+        hi = min(x.shape[0], lo + step)
+        st.append(x[lo:hi], z["prio"][lo:hi], z["tagmask"][lo:hi], z["expires_us"][lo:hi])
+    check(st._lib.pilott_mem_set_option(st._h, 7, max(total, st.count)))
+    return st
+
+
 def topk_merge(idx, score64, k: Optional[int] = None):
     """[shards, nq, k] per-shard results -> global top-k (device tensors)."""
     torch = _torch()

@@ -222,3 +222,21 @@ def test_full_size_properties(torch_cuda):
     oidx, osc = retrieval_c.search(os_, q[sample], 10)
     assert np.array_equal(idx[sample], oidx) and np.array_equal(sc64[sample], osc)
     gs.close()
+
+
+def test_snapshot_round_trip(torch_cuda, tmp_path):
+    from pilottai_b200.store import load_snapshot, save_snapshot
+    gs, os_, x = _fill(3000, 200, 2048, seed=17, chunks=5)            # ring wrapped: 3000 rows into 2048 slots
+    q = synth.queries(11, 200, seed=18)
+    want = gs.search(q, 10, want_score64=True, min_priority=1, now_us=1_000_000)
+    path = str(tmp_path / "snap")
+    save_snapshot(gs, path)
+    gs2 = load_snapshot(path)
+    assert gs2.info() == gs.info()
+    got = gs2.search(q, 10, want_score64=True, min_priority=1, now_us=1_000_000)
+    for w, g in zip(want, got):
+        assert np.array_equal(w, g)                                   # same sequence numbers, same bits
+    ea, eb = gs.export(), gs2.export()
+    for key in ea:
+        assert np.array_equal(ea[key], eb[key]), key
+    gs.close(); gs2.close()
