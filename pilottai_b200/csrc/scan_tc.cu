@@ -309,9 +309,12 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                         tma_load_2d(sa, &map_q, kb * BK, (int)q0, bar_full + 8 * stage);
                         tma_load_2d(sb, &map_c, kb * BK, n0, bar_full + 8 * stage);
                     } else {
-                        if (leader) mbar_arrive_expect_tx(bar_full + 8 * stage, 2 * Cfg::STAGE_BYTES);
+                        // dbg & 64: traffic experiment -- skip the corpus (B) load on odd k-blocks (stale
+                        // data, wrong results) to see how much of the mainloop time is L2 -> SM supply
+                        const bool skip_b = (dbg & 64) && (kb & 1);
+                        if (leader) mbar_arrive_expect_tx(bar_full + 8 * stage, skip_b ? 2 * Cfg::A_BYTES : 2 * Cfg::STAGE_BYTES);
                         tma_load_2d_cg2(sa, &map_q, kb * BK, (int)q0, full0 + 8 * stage);
-                        tma_load_2d_cg2(sb, &map_c, kb * BK, n0, full0 + 8 * stage);
+                        if (!skip_b) tma_load_2d_cg2(sb, &map_c, kb * BK, n0, full0 + 8 * stage);
                     }
                     if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
                 }
@@ -362,7 +365,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
         uint64_t* rows = bufs + ((size_t)set * BM + quarter * 32) * CAPT;
         uint64_t* mine = bufs + ((size_t)set * BM + row) * CAPT;
         const uint32_t head32 = (uint32_t)head, cap32 = (uint32_t)capacity;
-        float thr = -INFINITY;
+        float thr = (dbg & 128) ? INFINITY : -INFINITY;   // dbg & 128: fast path only (no candidate ever passes)
         int cnt = 0, conv = 0;
         const int64_t qrow = q0 + row;
         const bool has_q = qrow < nq;
