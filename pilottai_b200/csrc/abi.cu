@@ -243,10 +243,14 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
         rc = h->partials.ensure((size_t)nq * lists * KP_HOST * 8);
         if (rc) return rc;
         a.partials = (uint64_t*)h->partials.p;
-        rc = h->gthr.ensure((size_t)nq * 4);
+        const size_t nq32 = (size_t)round_up(nq, 32);           // keeps the [nq][32] block 128-byte aligned
+        rc = h->gthr.ensure((nq32 + (size_t)nq * 32) * 4);      // [nq] thresholds + [nq][32] first-tile list maxima
         if (rc) return rc;
         a.gthr = (uint32_t*)h->gthr.p;
-        CK(cudaMemsetAsync(a.gthr, 0, (size_t)nq * 4, st));
+        a.gmax = a.gthr + nq32;
+        a.krank = k + 6 <= 16 ? 16 : 32;
+        f.gthr = a.gthr;
+        CK(cudaMemsetAsync(a.gthr, 0, (nq32 + (size_t)nq * 32) * 4, st));
         cudaEvent_t e1 = nullptr;
         rc = profile_begin(h, st, &e1);
         if (rc) return rc;

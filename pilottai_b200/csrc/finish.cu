@@ -119,7 +119,8 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_l
               int64_t head, int64_t base_seq, int64_t seq_mul, int64_t seq_add, int k, double err,
               int64_t* __restrict__ out_idx,
               float* __restrict__ out_score, double* __restrict__ out_score64,
-              uint8_t* __restrict__ flags, int32_t* __restrict__ inexact, int stage_rows) {
+              uint8_t* __restrict__ flags, int32_t* __restrict__ inexact, int stage_rows,
+              const uint32_t* __restrict__ gthr) {
     extern __shared__ __align__(16) unsigned char s_rows[];     // [pool_n + 1][ld*2 + 16] when stage_rows
     __shared__ uint64_t s_pool[FIN_WARPS][32];
     __shared__ uint64_t s_bound[FIN_WARPS];
@@ -200,6 +201,11 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_l
     if (warp != 0) return;
     const uint64_t worst = shfl64(best, pool_n - 1);
     if (worst != 0ull && worst > bound) bound = worst;     // the pool itself is full
+    if (gthr) {                                            // rows dropped by a threshold scored below it
+        const uint32_t g = __ldcg(gthr + q);
+        const uint64_t gk = ((uint64_t)g << 32) | 0xFFFFFFFFull;
+        if (g != 0u && gk > bound) bound = gk;
+    }
     const bool pool_full = bound != 0ull;                  // something may have been dropped
     // 3. exact re-score
     const bool valid = best != 0ull;
@@ -250,7 +256,7 @@ cudaError_t launch_finish(const FinishArgs& a, cudaStream_t st) {
         a.partials, a.slots, a.list_len, a.pool_n, a.rows_per_group, a.lists_base, a.groups_rem, a.lists_extra,
         (const __nv_bfloat16*)a.qb, (const __nv_bfloat16*)a.vec, a.ld, a.nq,
         a.capacity, a.head, a.base_seq, a.seq_mul, a.seq_add, a.k, a.err, a.out_idx, a.out_score, a.out_score64,
-        a.flags, a.inexact, stage_rows);
+        a.flags, a.inexact, stage_rows, a.gthr);
     return cudaGetLastError();
 }
 

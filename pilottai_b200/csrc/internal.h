@@ -13,6 +13,7 @@ struct ScanArgs {
     const float* tile_max;   // [cap_pad/256]: largest valid scale of each 256-row tile
     uint64_t* partials;      // [nq][slots][KP] candidate keys
     uint32_t* gthr;          // [nq] shared per-query threshold (ordered-uint score), zeroed per search
+    uint32_t* gmax;          // [nq][32] first-tile maximum of each candidate list (ordered-uint), zeroed per search
     int64_t nq;
     int64_t nslots;          // physical slots holding rows (= min(total, capacity))
     int64_t capacity;
@@ -21,6 +22,7 @@ struct ScanArgs {
     int slots;               // work units per query group (base count)
     int slots_rem;           // this many groups (the first ones) get one more unit
     int list_len;            // candidates per list the scan writes (16 or 32)
+    int krank;               // rank of the first-tile list maxima used as cold-start threshold (16 or 32)
     int dbg;                 // developer switches for the tcgen05 kernel (0 in production)
 };
 
@@ -49,6 +51,7 @@ cudaError_t launch_scale(const float* inv_norm, const int32_t* prio, const uint6
 struct FinishArgs {
     const uint64_t* partials; int slots; int list_len;   // slots = allocated lists per query
     int pool_n;                 // survivors re-scored exactly (32)
+    const uint32_t* gthr;       // [nq] largest threshold any list of the query ended with (may be NULL)
     int rows_per_group, lists_base, groups_rem, lists_extra;  // lists of query q: lists_base + (q/rows_per_group < groups_rem ? lists_extra : 0)
     const void* qb; const void* vec; int ld;
     int64_t nq, capacity, head, base_seq;

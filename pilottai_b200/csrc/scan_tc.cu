@@ -36,6 +36,7 @@ constexpr int EPI_SETS = 2;    // one per accumulator stage
 constexpr int CAPT = 46;       // per-row candidate buffer: KP survivors + pending appends (smem budget)
 constexpr int TC_THREADS = 128 + EPI_SETS * 128;
 constexpr int PF_TILES = 0;     // corpus tiles prefetched into L2 ahead of the TMA loads (0: off -- measured no gain)
+constexpr int GMAX_LISTS = 32;  // lists per query that publish their first-tile maximum (cold-start threshold)
 constexpr int SC_RING = 4;     // staged scale tiles in flight (full/empty mbarrier pair per slot)
 
 template <int CG> struct TcCfg {
@@ -217,6 +218,31 @@ __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
+// Sorts 32 values held in registers into descending order (bitonic network, every index a
+// compile-time constant) and returns the one of rank `kth` (0 = largest).
+__device__ __forceinline__ uint32_t kth_largest_of_32(uint32_t (&v)[32], int kth) {
+#pragma unroll
+    for (int k = 2; k <= 32; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                const int l = i ^ j;
+                if (l > i) {
+                    const bool desc = (i & k) == 0;
+                    const uint32_t lo = min(v[i], v[l]), hi = max(v[i], v[l]);
+                    v[i] = desc ? hi : lo;
+                    v[l] = desc ? lo : hi;
+                }
+            }
+        }
+    }
+    uint32_t r = v[0];
+#pragma unroll
+    for (int i = 1; i < 32; ++i) r = (i == kth) ? v[i] : r;
+    return r;
+}
+
 // ---- the kernel ------------------------------------------------------------------------
 // Grid: `units` work units (CTAs for CG=1, CTA pairs for CG=2).  Unit u serves query group
 // u % groups (BM*CG query rows) and slot u / groups of that group.
@@ -224,7 +250,7 @@ template <int CG, int KPT>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_c,
                const float* __restrict__ scale, const float* __restrict__ tile_max,
-               uint64_t* __restrict__ partials, uint32_t* __restrict__ gthr, int64_t nq, int64_t nslots, int64_t capacity, int64_t head, int kblocks, int slots, int slots_rem, int groups, int dbg) {
+               uint64_t* __restrict__ partials, uint32_t* __restrict__ gthr, uint32_t* __restrict__ gmax, int64_t nq, int64_t nslots, int64_t capacity, int64_t head, int kblocks, int slots, int slots_rem, int groups, int krank, int dbg) {
     using Cfg = TcCfg<CG>;
     extern __shared__ unsigned char smem_dyn[];
     const uint32_t base = (smem_u32(smem_dyn) + 1023u) & ~1023u;        // 1024-B aligned (swizzle atom)
@@ -371,6 +397,11 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
         const bool has_q = qrow < nq;
         uint32_t aphase = 0;
         int as = 0;
+        // cold-start protocol needs at least `krank` publishing lists for this query (krank = rank of
+        // the list maxima used as threshold: comfortably below the k results the caller wants)
+        const int nlists_q = min(slots_g * EPI_SETS, GMAX_LISTS);
+        const bool cold = nlists_q >= krank && !(dbg & 16);
+        const int cold_need = max(krank, nlists_q - 4);
         long long w_tfull = 0, t_start = clock64();
         int n_prune = 0, n_slow = 0;
         long long t_prune = 0, t_slow = 0, t_loop = 0, t_early = 0;
@@ -391,6 +422,57 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
             tc_fence_after();
             if (g > f2ord(thr)) thr = ord2f(g);
             const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
+            // ---- cold start (first tile only) -------------------------------------------------
+            // With thr = -inf every element of the first tiles is a candidate and every row prunes
+            // again and again while the MMA pipe waits.  Instead: pass A only takes this list's best
+            // score over the tile (no candidates kept) and publishes it; the krank-th largest of the
+            // maxima published by the other CTAs sweeping the same query is a valid lower bound of
+            // the query's global krank-th best (krank distinct rows reach it), so it becomes the initial
+            // threshold; pass B is the normal scan of the same (still resident) accumulator tile.
+            if (ti == 0 && cold && !(dbg & 1)) {
+                float rowmax = -INFINITY;
+#pragma unroll 1
+                for (int c = set * CPS; c < (set + 1) * CPS; c += 16) {
+                    uint32_t v[16];
+                    tmem_ld16_issue(taddr0 + c, v);
+                    float sc[16];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const float4 f = *reinterpret_cast<const float4*>(scb + c + 4 * j);
+                        sc[4 * j] = f.x; sc[4 * j + 1] = f.y; sc[4 * j + 2] = f.z; sc[4 * j + 3] = f.w;
+                    }
+                    tmem_ld_wait(v);
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) rowmax = fmaxf(rowmax, __uint_as_float(v[j]) * sc[j]);
+                }
+                const int my_list = slot * EPI_SETS + set;
+                if (my_list < GMAX_LISTS && has_q && rowmax > -INFINITY) {
+                    gmax[qrow * GMAX_LISTS + my_list] = f2ord(rowmax);
+                    __threadfence();
+                }
+                uint32_t vals[32];
+                for (int attempt = 0; attempt < 64; ++attempt) {
+                    int have = 0;
+                    if (has_q) {
+                        const uint4* gp = reinterpret_cast<const uint4*>(gmax + qrow * GMAX_LISTS);
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) {
+                            const uint4 w4 = __ldcg(gp + u);
+                            vals[4 * u] = w4.x; vals[4 * u + 1] = w4.y; vals[4 * u + 2] = w4.z; vals[4 * u + 3] = w4.w;
+                        }
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) have += vals[i] != 0u;
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) vals[i] = 0u;
+                        have = 32;
+                    }
+                    if (__all_sync(FULL, have >= cold_need)) break;      // enough lists have published
+                    __nanosleep(256);
+                }
+                const uint32_t tk = kth_largest_of_32(vals, krank - 1);
+                if (tk != 0u && ord2f(tk) > thr) thr = ord2f(tk);
+            }
             // One 16-column chunk: scale, test groups of 4 (one FMNMX tree + compare + vote per group;
             // fmaxf drops NaN = filtered rows), append on the rare hit, prune full rows.
             auto load_scale = [&](float (&sc)[16], const int c) {
@@ -492,6 +574,9 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                    (int)blockIdx.x, warp, clock64() - t_start, w_tfull, t_loop, t_slow, n_slow, t_prune, n_prune, t_early, n_early);
         // flush: final prune of every row (four at a time), write this (slot, set) candidate list
         warp_prune_all_rows<CAPT, KPT>(rows, lane, cnt, conv, thr, head32, cap32);
+        // every row this list ever dropped scored below its final threshold: finish_kernel's gap check
+        // needs the largest of them per query
+        if (has_q && thr > -INFINITY) atomicMax(gthr + qrow, f2ord(thr));
         for (int r = 0; r < 32; ++r) {
             const int c = __shfl_sync(FULL, cnt, r);
             const int64_t q = q0 + quarter * 32 + r;
@@ -546,8 +631,8 @@ static cudaError_t launch_one(const ScanArgs& a, const CUtensorMap* map_q, const
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, scan_tc_kernel<CG, KPT>, *map_q, *map_c, a.scale, a.tile_max, a.partials, a.gthr,
-                              a.nq, a.nslots, a.capacity, a.head, kblocks, a.slots, a.slots_rem, groups, a.dbg);
+    return cudaLaunchKernelEx(&cfg, scan_tc_kernel<CG, KPT>, *map_q, *map_c, a.scale, a.tile_max, a.partials, a.gthr, a.gmax,
+                              a.nq, a.nslots, a.capacity, a.head, kblocks, a.slots, a.slots_rem, groups, a.krank, a.dbg);
 }
 
 cudaError_t scan_tc_init() {
