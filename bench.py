@@ -138,8 +138,12 @@ def run_ours(args):
                          "(use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    # stdout carries exactly one JSON line: anything libraries print there (NCCL's version banner)
+    # is sent to stderr for the whole run; the line itself goes to the saved descriptor.
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
-        os.environ.setdefault("NCCL_DEBUG", "WARN")       # keep NCCL's version banner off stdout (one JSON line only)
         dist.init_process_group("nccl", device_id=dev)
     if args.gpus != world:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run")
@@ -288,7 +292,8 @@ def run_ours(args):
             "e2e": {"value": e2e_value, "unit": "queries/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
         }
-        print(json.dumps(line), flush=True)
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     store.close()
     if world > 1:
         dist.destroy_process_group()
@@ -301,7 +306,13 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="1m", choices=["1m", "10m"],
+                    help="1m = BASELINE configs[1] (default, the headline); 10m = configs[2]: 10M x 1024 row-sharded")
     args = ap.parse_args()
+    if args.workload == "10m":
+        global N_ROWS, DIM, WORKLOAD
+        N_ROWS, DIM = 10_000_000, 1024
+        WORKLOAD = "semantic retrieval 10M entries x 1024-d bf16 row-sharded, 1024-query batches, top-10"
     if args.warmup < 3:
         args.warmup = 3
     if args.impl == "reference":
