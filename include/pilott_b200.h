@@ -89,7 +89,8 @@ int pilott_mem_append_host(pilott_mem_t* h, const float* x_host, int64_t n,
  *   candidates: priority >= min_prio AND (tagmask & req_tagmask) == req_tagmask
  *               AND NOT (expires_us != 0 AND now_us > expires_us)
  *   score:      cosine over bf16-rounded inputs (exact fp64 re-score of the survivors of
- *               the tensor-core pass, accumulated d = 0..dim-1 in order)
+ *               the tensor-core pass: eight interleaved fp64 partial sums, fixed combining tree,
+ *               exactly as oracle/retrieval_oracle.py states)
  *   rank:       (score desc, insertion sequence asc); k results per query.
  * q is [nq, dim] fp32.  out_idx [nq,k] receives insertion sequence numbers (-1 = fewer than
  * k candidates), out_score [nq,k] fp32 (-inf padding), out_score64 [nq,k] fp64 may be NULL.

@@ -3,7 +3,8 @@
  * Same stated rule (see the Python file's header; parity unpinned by the
  * reference, whose search is a substring test at
  * pilott/memory/enhanced_memory.py:110):
- *   bf16 inputs, fp64 accumulation over d = 0..D-1 in order, cosine with
+ *   bf16 inputs, fp64 accumulation in eight interleaved partial sums (partial j takes
+ *   d = j, j+8, ... in ascending order) combined ((p0+p1)+(p2+p3))+((p4+p5)+(p6+p7)), cosine with
  *   den = sqrt(nq)*sqrt(nm), score = den > 0 ? dot/den : 0, rank by
  *   (score desc, insertion sequence asc), filter as enhanced_memory.py:118-131
  *   and expiry as :20-21.
@@ -22,27 +23,31 @@ static inline double bf2d(uint16_t b) {
     return (double)f;
 }
 
+static inline double tree8(const double* p) {
+    return ((p[0] + p[1]) + (p[2] + p[3])) + ((p[4] + p[5]) + (p[6] + p[7]));
+}
+
 /* scores[q*N + n] for all rows; ld = row stride of m in elements. */
 void oracle_exact_scores(const uint16_t* q, int64_t Q, const uint16_t* m, int64_t N,
                          int D, int64_t ld_q, int64_t ld_m, double* out) {
     double* qd = (double*)malloc(sizeof(double) * (size_t)D);
     for (int64_t qi = 0; qi < Q; ++qi) {
-        double nq = 0.0;
+        double pq[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         for (int d = 0; d < D; ++d) {
             qd[d] = bf2d(q[qi * ld_q + d]);
-            nq += qd[d] * qd[d];
+            pq[d & 7] += qd[d] * qd[d];
         }
-        const double sq = sqrt(nq);
+        const double sq = sqrt(tree8(pq));
         for (int64_t n = 0; n < N; ++n) {
             const uint16_t* row = m + n * ld_m;
-            double dot = 0.0, nm = 0.0;
+            double pd[8] = {0, 0, 0, 0, 0, 0, 0, 0}, pm[8] = {0, 0, 0, 0, 0, 0, 0, 0};
             for (int d = 0; d < D; ++d) {
                 const double v = bf2d(row[d]);
-                dot += qd[d] * v;
-                nm += v * v;
+                pd[d & 7] += qd[d] * v;
+                pm[d & 7] += v * v;
             }
-            const double den = sq * sqrt(nm);
-            out[qi * N + n] = den > 0.0 ? dot / den : 0.0;
+            const double den = sq * sqrt(tree8(pm));
+            out[qi * N + n] = den > 0.0 ? tree8(pd) / den : 0.0;
         }
     }
     free(qd);

@@ -19,9 +19,12 @@ reference DOES specify is followed here and cited line by line:
 THE STATED SCORING RULE (this build's definition, the GPU must reproduce it):
 
 1. Vectors are rounded fp32 -> bf16, round-to-nearest-even (NaN -> 0x7FFF).
-2. dot(q, m)  = sum over d = 0..D-1, IN THAT ORDER, of q_d*m_d accumulated in
-   IEEE fp64 (each bf16*bf16 product is exact in fp64, so FMA == mul+add).
-   nq = sum q_d*q_d, nm = sum m_d*m_d, same order, fp64.
+2. dot(q, m) is accumulated in IEEE fp64 in EIGHT INTERLEAVED PARTIAL SUMS: partial j takes
+   the terms q_d*m_d for d = j, j+8, j+16, ... in ascending order; the total is
+   ((p0+p1)+(p2+p3))+((p4+p5)+(p6+p7)).  (Each bf16*bf16 product is exact in fp64, so
+   FMA == mul+add; eight short chains instead of one long one let the device keep the
+   same fixed order at an eighth of the dependent latency.)
+   nq = sum q_d*q_d, nm = sum m_d*m_d, same scheme.
 3. den = sqrt(nq) * sqrt(nm)  (fp64, correctly rounded sqrt, then one multiply)
    score = dot / den  if den > 0 else 0.0          (fp64 divide)
 4. Rank candidates by (score descending, insertion sequence ascending); take k.
@@ -53,19 +56,23 @@ def bf16_bits_to_f32(b: np.ndarray) -> np.ndarray:
     return (np.ascontiguousarray(b, dtype=np.uint16).astype(np.uint32) << np.uint32(16)).view(np.float32)
 
 
+def _tree8(p):
+    return ((p[0] + p[1]) + (p[2] + p[3])) + ((p[4] + p[5]) + (p[6] + p[7]))
+
+
 def _seq_dot(a: np.ndarray, b: np.ndarray) -> np.ndarray:
-    """[Q,D] x [N,D] -> [Q,N] fp64, accumulated sequentially over d (rule 2)."""
-    acc = np.zeros((a.shape[0], b.shape[0]), dtype=np.float64)
+    """[Q,D] x [N,D] -> [Q,N] fp64: eight interleaved partial sums, each sequential (rule 2)."""
+    acc = np.zeros((8, a.shape[0], b.shape[0]), dtype=np.float64)
     for d in range(a.shape[1]):
-        acc += a[:, d, None] * b[None, :, d]
-    return acc
+        acc[d & 7] += a[:, d, None] * b[None, :, d]
+    return _tree8(acc)
 
 
 def _seq_sqnorm(a: np.ndarray) -> np.ndarray:
-    acc = np.zeros(a.shape[0], dtype=np.float64)
+    acc = np.zeros((8, a.shape[0]), dtype=np.float64)
     for d in range(a.shape[1]):
-        acc += a[:, d] * a[:, d]
-    return acc
+        acc[d & 7] += a[:, d] * a[:, d]
+    return _tree8(acc)
 
 
 def exact_scores(q_bits: np.ndarray, m_bits: np.ndarray) -> np.ndarray:

@@ -32,13 +32,54 @@ __device__ __forceinline__ void warp_sort_pairs(double& s, int64_t& q, int lane)
     }
 }
 
-// Exact cosine of one query / one row, fp64, d = 0..ld-1 in order (padding columns are
-// zeros and add exactly nothing).  Every lane computes its own row; the query is read
+// THE STATED SCORING RULE (oracle/retrieval_oracle.py): fp64, eight interleaved partial sums --
+// partial j accumulates the terms d = j, j+8, j+16, ... in ascending order -- combined as
+// ((p0+p1)+(p2+p3))+((p4+p5)+(p6+p7)).  bf16*bf16 products are exact in fp64, so FMA == mul+add.
+// Eight independent chains of length D/8 instead of one of length D: the same determinism with
+// an eighth of the dependent latency.  Padding columns are zeros and add exactly nothing.
+struct Acc8 {
+    double p[8];
+    __device__ __forceinline__ Acc8() {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) p[j] = 0.0;
+    }
+    __device__ __forceinline__ double total() const {
+        return __dadd_rn(__dadd_rn(__dadd_rn(p[0], p[1]), __dadd_rn(p[2], p[3])),
+                         __dadd_rn(__dadd_rn(p[4], p[5]), __dadd_rn(p[6], p[7])));
+    }
+};
+
+// One 16-byte chunk = elements d .. d+7 (d a multiple of 8): element e feeds partial e.
+__device__ __forceinline__ void acc_chunk(const uint4& qv, const uint4& mv, Acc8& dot, Acc8& nq, Acc8& nm) {
+    const uint32_t qw[4] = {qv.x, qv.y, qv.z, qv.w}, mw[4] = {mv.x, mv.y, mv.z, mv.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const double q0 = (double)__uint_as_float(qw[j] << 16);
+        const double q1 = (double)__uint_as_float(qw[j] & 0xffff0000u);
+        const double m0 = (double)__uint_as_float(mw[j] << 16);
+        const double m1 = (double)__uint_as_float(mw[j] & 0xffff0000u);
+        dot.p[2 * j] = __fma_rn(q0, m0, dot.p[2 * j]);
+        nq.p[2 * j] = __fma_rn(q0, q0, nq.p[2 * j]);
+        nm.p[2 * j] = __fma_rn(m0, m0, nm.p[2 * j]);
+        dot.p[2 * j + 1] = __fma_rn(q1, m1, dot.p[2 * j + 1]);
+        nq.p[2 * j + 1] = __fma_rn(q1, q1, nq.p[2 * j + 1]);
+        nm.p[2 * j + 1] = __fma_rn(m1, m1, nm.p[2 * j + 1]);
+    }
+}
+
+__device__ __forceinline__ double cosine_from(const Acc8& dot, const Acc8& nq, const Acc8& nm, double* nq_out) {
+    const double nqt = nq.total();
+    if (nq_out) *nq_out = nqt;
+    const double den = __dmul_rn(__dsqrt_rn(nqt), __dsqrt_rn(nm.total()));
+    return den > 0.0 ? __ddiv_rn(dot.total(), den) : 0.0;
+}
+
+// Exact cosine of one query / one row.  Every lane computes its own row; the query is read
 // through the read-only path (same address in all lanes -> broadcast).
 __device__ __forceinline__ double exact_cosine(const __nv_bfloat16* __restrict__ qrow,
                                                const __nv_bfloat16* __restrict__ mrow, int ld,
                                                double* nq_out = nullptr) {
-    double dot = 0.0, nq = 0.0, nm = 0.0;
+    Acc8 dot, nq, nm;
     for (int c = 0; c < ld; c += 32) {          // ld is a multiple of 64; 8 loads in flight per step
         uint4 qv[4], mv[4];
 #pragma unroll
@@ -47,22 +88,18 @@ __device__ __forceinline__ double exact_cosine(const __nv_bfloat16* __restrict__
             mv[u] = __ldg(reinterpret_cast<const uint4*>(mrow + c + 8 * u));
         }
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const uint32_t qw[4] = {qv[u].x, qv[u].y, qv[u].z, qv[u].w}, mw[4] = {mv[u].x, mv[u].y, mv[u].z, mv[u].w};
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const double q0 = (double)__uint_as_float(qw[j] << 16);
-                const double q1 = (double)__uint_as_float(qw[j] & 0xffff0000u);
-                const double m0 = (double)__uint_as_float(mw[j] << 16);
-                const double m1 = (double)__uint_as_float(mw[j] & 0xffff0000u);
-                dot = __fma_rn(q0, m0, dot); nq = __fma_rn(q0, q0, nq); nm = __fma_rn(m0, m0, nm);
-                dot = __fma_rn(q1, m1, dot); nq = __fma_rn(q1, q1, nq); nm = __fma_rn(m1, m1, nm);
-            }
-        }
+        for (int u = 0; u < 4; ++u) acc_chunk(qv[u], mv[u], dot, nq, nm);
     }
-    if (nq_out) *nq_out = nq;
-    const double den = __dmul_rn(__dsqrt_rn(nq), __dsqrt_rn(nm));
-    return den > 0.0 ? __ddiv_rn(dot, den) : 0.0;
+    return cosine_from(dot, nq, nm, nq_out);
+}
+
+// Same arithmetic, operands staged in shared memory (generic pointers).
+__device__ __forceinline__ double exact_cosine_smem(const unsigned char* qrow, const unsigned char* mrow,
+                                                    int ld, double* nq_out) {
+    Acc8 dot, nq, nm;
+    for (int c = 0; c < ld; c += 8)
+        acc_chunk(*reinterpret_cast<const uint4*>(qrow + 2 * c), *reinterpret_cast<const uint4*>(mrow + 2 * c), dot, nq, nm);
+    return cosine_from(dot, nq, nm, nq_out);
 }
 
 // Sorts a bitonic sequence (one key per lane) into descending order: 5 compare-exchange steps.
@@ -75,29 +112,6 @@ __device__ __forceinline__ uint64_t warp_bitonic_merge_desc(uint64_t v, int lane
         v = lower ? mx : mn;
     }
     return v;
-}
-
-// Same arithmetic as exact_cosine, operands staged in shared memory (generic pointers).
-__device__ __forceinline__ double exact_cosine_smem(const unsigned char* qrow, const unsigned char* mrow,
-                                                    int ld, double* nq_out) {
-    double dot = 0.0, nq = 0.0, nm = 0.0;
-    for (int c = 0; c < ld; c += 8) {
-        const uint4 qv = *reinterpret_cast<const uint4*>(qrow + 2 * c);
-        const uint4 mv = *reinterpret_cast<const uint4*>(mrow + 2 * c);
-        const uint32_t qw[4] = {qv.x, qv.y, qv.z, qv.w}, mw[4] = {mv.x, mv.y, mv.z, mv.w};
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const double q0 = (double)__uint_as_float(qw[j] << 16);
-            const double q1 = (double)__uint_as_float(qw[j] & 0xffff0000u);
-            const double m0 = (double)__uint_as_float(mw[j] << 16);
-            const double m1 = (double)__uint_as_float(mw[j] & 0xffff0000u);
-            dot = __fma_rn(q0, m0, dot); nq = __fma_rn(q0, q0, nq); nm = __fma_rn(m0, m0, nm);
-            dot = __fma_rn(q1, m1, dot); nq = __fma_rn(q1, q1, nq); nm = __fma_rn(m1, m1, nm);
-        }
-    }
-    *nq_out = nq;
-    const double den = __dmul_rn(__dsqrt_rn(nq), __dsqrt_rn(nm));
-    return den > 0.0 ? __ddiv_rn(dot, den) : 0.0;
 }
 
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
@@ -123,6 +137,7 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_l
               const uint32_t* __restrict__ gthr) {
     extern __shared__ __align__(16) unsigned char s_rows[];     // [pool_n + 1][ld*2 + 16] when stage_rows
     __shared__ uint64_t s_pool[FIN_WARPS][32];
+    __shared__ double s_part[3][FIN_WARPS][32];              // per-warp pair sums of (dot, nq, nm) per candidate
     __shared__ uint64_t s_bound[FIN_WARPS];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t q = blockIdx.x;
@@ -197,6 +212,29 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_l
         asm volatile("cp.async.commit_group;" ::: "memory");
         asm volatile("cp.async.wait_group 0;" ::: "memory");
         __syncthreads();
+        // 3a. exact re-score, split over the four warps: lane = candidate, warp w owns partial sums
+        //     2w and 2w+1 of the stated rule (elements d = 2w, 2w+1 mod 8, i.e. word w of every
+        //     16-byte chunk), so each warp walks a quarter of the elements.  The pair sum
+        //     p[2w] + p[2w+1] is formed here; warp 0 finishes the fixed tree (s0+s1)+(s2+s3).
+        {
+            const unsigned char* qrow_s = s_rows + pool_n * row_bytes;
+            const unsigned char* mrow_s = s_rows + lane * row_bytes;
+            double d0 = 0.0, d1 = 0.0, a0 = 0.0, a1 = 0.0, b0 = 0.0, b1 = 0.0;
+            if (s_pool[0][lane] != 0ull) {
+                for (int c = 0; c < ld; c += 8) {
+                    const uint32_t qw = *reinterpret_cast<const uint32_t*>(qrow_s + 2 * c + 4 * warp);
+                    const uint32_t mw = *reinterpret_cast<const uint32_t*>(mrow_s + 2 * c + 4 * warp);
+                    const double q0 = (double)__uint_as_float(qw << 16), q1 = (double)__uint_as_float(qw & 0xffff0000u);
+                    const double m0 = (double)__uint_as_float(mw << 16), m1 = (double)__uint_as_float(mw & 0xffff0000u);
+                    d0 = __fma_rn(q0, m0, d0); a0 = __fma_rn(q0, q0, a0); b0 = __fma_rn(m0, m0, b0);
+                    d1 = __fma_rn(q1, m1, d1); a1 = __fma_rn(q1, q1, a1); b1 = __fma_rn(m1, m1, b1);
+                }
+            }
+            s_part[0][warp][lane] = __dadd_rn(d0, d1);
+            s_part[1][warp][lane] = __dadd_rn(a0, a1);
+            s_part[2][warp][lane] = __dadd_rn(b0, b1);
+        }
+        __syncthreads();
     }
     if (warp != 0) return;
     const uint64_t worst = shfl64(best, pool_n - 1);
@@ -217,8 +255,15 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_l
         const uint32_t age = key_age(best);
         int64_t slot = head + age;
         if (slot >= capacity) slot -= capacity;
-        sc = stage_rows ? exact_cosine_smem(s_rows + pool_n * row_bytes, s_rows + lane * row_bytes, ld, &nqn)
-                        : exact_cosine(qrow, vec + slot * ld, ld, &nqn);
+        if (stage_rows) {
+            const double dt = __dadd_rn(__dadd_rn(s_part[0][0][lane], s_part[0][1][lane]), __dadd_rn(s_part[0][2][lane], s_part[0][3][lane]));
+            nqn = __dadd_rn(__dadd_rn(s_part[1][0][lane], s_part[1][1][lane]), __dadd_rn(s_part[1][2][lane], s_part[1][3][lane]));
+            const double nmt = __dadd_rn(__dadd_rn(s_part[2][0][lane], s_part[2][1][lane]), __dadd_rn(s_part[2][2][lane], s_part[2][3][lane]));
+            const double den = __dmul_rn(__dsqrt_rn(nqn), __dsqrt_rn(nmt));
+            sc = den > 0.0 ? __ddiv_rn(dt, den) : 0.0;
+        } else {
+            sc = exact_cosine(qrow, vec + slot * ld, ld, &nqn);
+        }
         seq = base_seq + age;
     }
     // 4. final order
