@@ -208,10 +208,16 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
     const int64_t nq_pad = round_up(nq, 256);
     int rc = h->qbuf.ensure((size_t)nq_pad * h->ld * 2);
     if (rc) return rc;
-    CK(pilott::launch_convert_queries(q_dev, nq, h->dim, h->ld, h->qbuf.p, st));
-    CK(pilott::launch_scale(h->inv_norm, h->prio, h->tagmask, h->expires, h->count, h->cap_pad,
-                            min_prio, req, now_us, h->scale, h->tile_max, st));
-    h->launches += 2;
+    // per-search words every scan variant may use: [nq] shared thresholds + [nq][32] first-tile maxima
+    const size_t nq32 = (size_t)round_up(nq, 32);           // keeps the [nq][32] block 128-byte aligned
+    const size_t n_words = nq32 + (size_t)nq * 32;
+    rc = h->gthr.ensure(n_words * 4);
+    if (rc) return rc;
+    // one launch: query conversion + scale pre-pass + zeroing of those words and of the inexact counter
+    CK(pilott::launch_prepare(q_dev, nq, h->dim, h->ld, h->qbuf.p, h->inv_norm, h->prio, h->tagmask, h->expires,
+                              h->count, h->capacity, h->cap_pad, min_prio, req, now_us, h->scale, h->tile_max,
+                              (uint32_t*)h->gthr.p, (int64_t)n_words, out_inexact, st));
+    h->launches += 1;
 
     int kern = pick_kernel(h);
     const int ctas = h->opt_ctas > 0 ? h->opt_ctas : h->num_sms;
@@ -243,14 +249,10 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
         rc = h->partials.ensure((size_t)nq * lists * KP_HOST * 8);
         if (rc) return rc;
         a.partials = (uint64_t*)h->partials.p;
-        const size_t nq32 = (size_t)round_up(nq, 32);           // keeps the [nq][32] block 128-byte aligned
-        rc = h->gthr.ensure((nq32 + (size_t)nq * 32) * 4);      // [nq] thresholds + [nq][32] first-tile list maxima
-        if (rc) return rc;
         a.gthr = (uint32_t*)h->gthr.p;
         a.gmax = a.gthr + nq32;
         a.krank = k + 6 <= 16 ? 16 : 32;
         f.gthr = a.gthr;
-        CK(cudaMemsetAsync(a.gthr, 0, (nq32 + (size_t)nq * 32) * 4, st));
         cudaEvent_t e1 = nullptr;
         rc = profile_begin(h, st, &e1);
         if (rc) return rc;
@@ -269,7 +271,6 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
         CK(pilott::launch_scan_generic(a, h->num_sms, st));
         if (e1) CK(cudaEventRecord(e1, st));
     }
-    if (out_inexact) CK(cudaMemsetAsync(out_inexact, 0, 4, st));
     f.partials = a.partials; f.slots = lists; f.list_len = a.list_len; f.qb = h->qbuf.p; f.vec = h->vec; f.ld = h->ld;
     f.pool_n = 32;   // always re-score 32 survivors: a wide margin below the k-th keeps the gap check quiet at 10M+ rows
     f.nq = nq; f.capacity = h->capacity; f.head = h->head; f.base_seq = h->total - h->count;

@@ -48,6 +48,12 @@ cudaError_t launch_scale(const float* inv_norm, const int32_t* prio, const uint6
                          const int64_t* expires, int64_t nslots, int64_t cap_pad, int32_t min_prio,
                          uint64_t req, int64_t now_us, float* scale, float* tile_max, cudaStream_t st);
 
+cudaError_t launch_prepare(const float* q, int64_t nq, int dim, int ld, void* qb, const float* inv_norm,
+                           const int32_t* prio, const uint64_t* tagmask, const int64_t* expires, int64_t nslots,
+                           int64_t capacity, int64_t cap_pad, int32_t min_prio, uint64_t req, int64_t now_us,
+                           float* scale, float* tile_max, uint32_t* zero_words, int64_t n_zero_words,
+                           int32_t* inexact, cudaStream_t st);
+
 struct FinishArgs {
     const uint64_t* partials; int slots; int list_len;   // slots = allocated lists per query
     int pool_n;                 // survivors re-scored exactly (32)

@@ -111,6 +111,87 @@ scale_kernel(const float* __restrict__ inv_norm, const int32_t* __restrict__ pri
     }
 }
 
+// One 256-row tile of the scale pre-pass by ONE warp (8 rows per lane, 16-byte loads when the
+// whole tile lies inside the columns), same results as scale_kernel.
+__device__ __forceinline__ void scale_tile_warp(const float* __restrict__ inv_norm, const int32_t* __restrict__ prio,
+                                                const uint64_t* __restrict__ tagmask, const int64_t* __restrict__ expires,
+                                                int64_t nslots, int64_t capacity, int32_t min_prio, uint64_t req,
+                                                int64_t now_us, float* __restrict__ scale, float* __restrict__ tile_max,
+                                                int64_t t, int lane) {
+    const float qnan = __int_as_float(0x7fc00000);
+    const int64_t n0 = t * 256 + lane * 8;
+    float s[8];
+    if (t * 256 + 256 <= capacity) {
+        const float4 i0 = __ldg(reinterpret_cast<const float4*>(inv_norm + n0)), i1 = __ldg(reinterpret_cast<const float4*>(inv_norm + n0 + 4));
+        const int4 p0 = __ldg(reinterpret_cast<const int4*>(prio + n0)), p1 = __ldg(reinterpret_cast<const int4*>(prio + n0 + 4));
+        const float iv[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
+        const int pv[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const ulonglong2 tg = __ldg(reinterpret_cast<const ulonglong2*>(tagmask + n0 + 2 * j));
+            const longlong2 ex = __ldg(reinterpret_cast<const longlong2*>(expires + n0 + 2 * j));
+            const uint64_t tv[2] = {tg.x, tg.y};
+            const int64_t ev[2] = {ex.x, ex.y};
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                const int e = 2 * j + u;
+                const bool ok = n0 + e < nslots && pv[e] >= min_prio && (tv[u] & req) == req && !(ev[u] != 0 && now_us > ev[u]);
+                s[e] = ok ? iv[e] : qnan;
+            }
+        }
+    } else {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const int64_t n = n0 + e;
+            s[e] = qnan;
+            if (n < nslots) {
+                const int64_t ex = expires[n];
+                if (prio[n] >= min_prio && (tagmask[n] & req) == req && !(ex != 0 && now_us > ex)) s[e] = inv_norm[n];
+            }
+        }
+    }
+    *reinterpret_cast<float4*>(scale + n0) = make_float4(s[0], s[1], s[2], s[3]);
+    *reinterpret_cast<float4*>(scale + n0 + 4) = make_float4(s[4], s[5], s[6], s[7]);
+    float m = -INFINITY;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) m = fmaxf(m, s[e]);                 // fmaxf ignores NaN
+#pragma unroll
+    for (int j = 16; j > 0; j >>= 1) m = fmaxf(m, __shfl_xor_sync(FULL, m, j));
+    if (lane == 0) tile_max[t] = m;
+}
+
+// Everything a fused search needs before the scan, in ONE launch: query conversion (one warp per
+// query row), the scale pre-pass (one warp per 256-row tile) and the zeroing of the per-search
+// words (shared thresholds, first-tile list maxima, the inexact counter).
+__global__ void __launch_bounds__(256)
+prepare_kernel(const float* __restrict__ q, int64_t nq, int dim, int ld, __nv_bfloat16* __restrict__ qb,
+               const float* __restrict__ inv_norm, const int32_t* __restrict__ prio,
+               const uint64_t* __restrict__ tagmask, const int64_t* __restrict__ expires, int64_t nslots,
+               int64_t capacity, int64_t cap_pad, int32_t min_prio, uint64_t req, int64_t now_us,
+               float* __restrict__ scale, float* __restrict__ tile_max, uint32_t* __restrict__ zero_words,
+               int64_t n_zero_words, int32_t* __restrict__ inexact) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    const int64_t ntiles = cap_pad / 256;
+    const int64_t nzero = (n_zero_words + 127) / 128;               // 128 words (512 B) per item
+    const int64_t items = nq + ntiles + nzero;
+    if (warp == 0 && lane == 0 && inexact) *inexact = 0;
+    for (int64_t it = warp; it < items; it += nwarps) {
+        if (it < nq) {
+            convert_row(q + it * dim, qb + it * ld, dim, ld, lane);
+        } else if (it < nq + ntiles) {
+            scale_tile_warp(inv_norm, prio, tagmask, expires, nslots, capacity, min_prio, req, now_us, scale, tile_max,
+                            it - nq, lane);
+        } else {
+            const int64_t w0 = (it - nq - ntiles) * 128 + lane * 4;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (w0 + j < n_zero_words) zero_words[w0 + j] = 0u;
+        }
+    }
+}
+
 // keep[i] for the i-th oldest held row (age order): not expired at now_us.
 __global__ void __launch_bounds__(256)
 compact_flags_kernel(const int64_t* __restrict__ expires, int64_t count, int64_t head,
@@ -176,6 +257,18 @@ cudaError_t launch_scale(const float* inv_norm, const int32_t* prio, const uint6
                          uint64_t req, int64_t now_us, float* scale, float* tile_max, cudaStream_t st) {
     scale_kernel<<<grid_for(cap_pad, 256, 148 * 8), 256, 0, st>>>(
         inv_norm, prio, tagmask, expires, nslots, cap_pad, min_prio, req, now_us, scale, tile_max);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_prepare(const float* q, int64_t nq, int dim, int ld, void* qb, const float* inv_norm,
+                           const int32_t* prio, const uint64_t* tagmask, const int64_t* expires, int64_t nslots,
+                           int64_t capacity, int64_t cap_pad, int32_t min_prio, uint64_t req, int64_t now_us,
+                           float* scale, float* tile_max, uint32_t* zero_words, int64_t n_zero_words,
+                           int32_t* inexact, cudaStream_t st) {
+    const int64_t items = nq + cap_pad / 256 + (n_zero_words + 127) / 128;
+    prepare_kernel<<<grid_for(items, 8, 148 * 8), 256, 0, st>>>(
+        q, nq, dim, ld, (__nv_bfloat16*)qb, inv_norm, prio, tagmask, expires, nslots, capacity, cap_pad, min_prio, req,
+        now_us, scale, tile_max, zero_words, n_zero_words, inexact);
     return cudaGetLastError();
 }
 
