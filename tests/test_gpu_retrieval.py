@@ -240,3 +240,29 @@ def test_snapshot_round_trip(torch_cuda, tmp_path):
     for key in ea:
         assert np.array_equal(ea[key], eb[key]), key
     gs.close(); gs2.close()
+
+
+@pytest.mark.parametrize("kernel", ["tc", "tc_pair"])
+def test_many_queries_multi_wave_grid(torch_cuda, kernel):
+    """More query groups than SMs: the scan grid runs in several waves, the lists of one query
+    are not all resident together, and the cold-start exchange must neither stall nor change
+    the result."""
+    gs, os_, x = _fill(20_000, 64, 20_000, seed=23, dup=0.002)
+    gs.set_kernel(kernel)
+    q = synth.queries(3000, 64, seed=24)
+    _check(gs, os_, q, 10)
+    _check(gs, os_, q[:700], 10, min_priority=2, req_tagmask=0b1, now_us=1_000_000)
+    gs.close()
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_wide_vectors_unstaged_rescore(torch_cuda, kernel):
+    """dim 1536: 24 k-blocks per tile, and the exact re-score reads the rows straight from HBM
+    (33 staged rows would not fit the finish kernel's shared memory)."""
+    gs, os_, x = _fill(3000, 1536, 4096, seed=25)
+    gs.set_kernel(kernel)
+    q = synth.queries(20, 1536, seed=26)
+    q[0] = x[1234]
+    _check(gs, os_, q, 10)
+    _check(gs, os_, q, 24, min_priority=1)
+    gs.close()
