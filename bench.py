@@ -257,7 +257,7 @@ def run_ours(args):
     alg_bytes = 2.0 * n_local * DIM + 4.0 * n_local + 2.0 * NQ * DIM + 12.0 * NQ * TOPK
     roofline = {"bound": "tensor", "achieved": achieved, "peak": peaks["tflops"], "unit": "TFLOP/s",
                 "frac": achieved / peaks["tflops"], "traffic": _traffic() if world == 1 else None,
-                "kernel": "scan_tc_kernel<2,16>", "kernel_ms": avg_scan_ms, "peak_source": peaks["src"],
+                "kernel": "scan_tc_kernel<2,8>", "kernel_ms": avg_scan_ms, "peak_source": peaks["src"],
                 "hbm_gbs": alg_bytes / (avg_scan_ms * 1e-3) / 1e9, "hbm_frac": alg_bytes / (avg_scan_ms * 1e-3) / 1e9 / peaks["hbm"]}
 
     # ---- CPU baseline (oracle port) on a bounded sample, rank 0, N = 1 only ----------------------

@@ -56,7 +56,7 @@ int pilott_mem_info(const pilott_mem_t* h, int64_t* total, int64_t* count, int64
 /* which = 0: scan kernel (0 auto, 1 generic CUDA-core, 2 tcgen05 1-CTA, 3 tcgen05 CTA-pair).
  * which = 1: CTAs used by the scan (0 = one per SM).
  * which = 2: developer switches (0 in production).
- * which = 3: candidates each partial list keeps: 0 auto (16 when k <= 12 or the scan produces >= 8 lists per query, else 32), 16, 32.
+ * which = 3: candidates each partial list keeps: 0 auto (8 when k <= 10 and the pair scan produces >= 16 lists per query; 16 when k <= 12 or >= 8 lists; else 32), 8, 16, 32.
  * which = 4: 1 = record CUDA events around the scan kernel (read with pilott_mem_profile_read).
  * which = 5 / 6: reported index = sequence * stride (5) + offset (6); a row-sharded store that
  *            holds global rows i with i % world == rank uses stride = world, offset = rank.

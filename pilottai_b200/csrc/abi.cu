@@ -133,7 +133,7 @@ struct pilott_mem {
     int opt_kernel = 0;     // 0 auto, 1 generic, 2 tc 1-CTA, 3 tc pair
     int opt_ctas = 0;
     int opt_dbg = 0;
-    int opt_list_len = 0;   // 0 auto (16 when k <= 12), 16, 32
+    int opt_list_len = 0;   // 0 auto, 8, 16, 32
     int64_t seq_mul = 1, seq_add = 0;   // reported index = seq * seq_mul + seq_add (row-sharded stores)
     bool profile = false;   // record CUDA events around the scan kernel
     std::vector<cudaEvent_t> ev;        // pairs: [2i] before, [2i+1] after
@@ -239,8 +239,11 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
         // 16-entry lists are enough whenever the lists together hold several times k candidates (the
         // gap check in finish_kernel catches the rare query whose top-k crowd into one list).
         const int nlists = (a.slots + (a.slots_rem > 0 ? 1 : 0)) * pilott::scan_tc_lists_per_slot();
+        // With 16+ lists and k <= 10, 8-entry lists do (and free shared memory for a fifth stage).
         const bool lists16 = k <= 12 || nlists >= 8;
-        a.list_len = (h->opt_list_len == 16 || (h->opt_list_len == 0 && lists16)) ? 16 : 32;
+        const bool lists8 = cg == 2 && k <= 10 && nlists >= 16;
+        if (h->opt_list_len == 8 || h->opt_list_len == 16 || h->opt_list_len == 32) a.list_len = h->opt_list_len;
+        else a.list_len = lists8 ? 8 : (lists16 ? 16 : 32);
         lists = (a.slots + (a.slots_rem > 0 ? 1 : 0)) * pilott::scan_tc_lists_per_slot();
         f.rows_per_group = pilott::scan_tc_rows_per_group(cg);
         f.lists_base = a.slots * pilott::scan_tc_lists_per_slot();
@@ -415,7 +418,7 @@ int pilott_mem_set_option(pilott_mem_t* h, int which, int64_t value) {
         if (value < 0) return fail(PILOTT_EINVAL, "sequence offset must be >= 0");
         h->seq_add = value;
     } else if (which == 3) {
-        if (value != 0 && value != 16 && value != 32) return fail(PILOTT_EINVAL, "list length must be 0, 16 or 32");
+        if (value != 0 && value != 8 && value != 16 && value != 32) return fail(PILOTT_EINVAL, "list length must be 0, 8, 16 or 32");
         h->opt_list_len = (int)value;
     } else if (which == 2) {
         h->opt_dbg = (int)value;      // developer switches (profiling experiments); 0 = off

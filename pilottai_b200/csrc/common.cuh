@@ -73,7 +73,7 @@ __device__ __forceinline__ uint64_t raw_to_key(uint64_t raw, uint32_t head, uint
     return (raw & 0xFFFFFFFF00000000ull) | (uint64_t)(0xFFFFFFFFu - (uint32_t)age);
 }
 
-// Keep the KPT (16 or 32) best of a row buffer holding cnt (<= CAPT <= 64) entries.  Whole
+// Keep the KPT (8, 16 or 32) best of a row buffer holding cnt (<= CAPT <= 64) entries.  Whole
 // warp cooperates.  Entries at index >= conv are still raw.  Leaves the survivors (unsorted,
 // empty = 0) in buf[0..KPT) and returns them per lane (lanes >= KPT return 0).
 template <int CAPT, int KPT>
@@ -84,11 +84,18 @@ __device__ __forceinline__ uint64_t warp_prune(uint64_t* buf, int cnt, int conv,
     if (lane < cnt && lane >= conv) a = raw_to_key(a, head, cap);
     if ((lane + 32) < cnt && (lane + 32) >= conv) b = raw_to_key(b, head, cap);
     a = warp_sort64<true>(a, lane);
-    b = warp_sort64<false>(b, lane);
-    uint64_t m = a > b ? a : b;                // half-cleaner of a bitonic sequence: the top 32
-    if (KPT == 16) {                           // one more half-cleaner step: top 16 in lanes 0..15
+    uint64_t m = a;
+    if (CAPT > 32) {                           // second half of the buffer exists
+        b = warp_sort64<false>(b, lane);
+        m = a > b ? a : b;                     // half-cleaner of a bitonic sequence: the top 32
+    }
+    if (KPT <= 16) {                           // one more half-cleaner step: top 16 in lanes 0..15
         const uint64_t o = shfl_xor64(m, 16);
         m = (lane < 16) ? (m > o ? m : o) : 0ull;
+    }
+    if (KPT == 8) {                            // and another: top 8 in lanes 0..7
+        const uint64_t o = shfl_xor64(m, 8);
+        m = (lane < 8) ? (m > o ? m : o) : 0ull;
     }
     uint64_t mn = m;
 #pragma unroll
@@ -138,14 +145,18 @@ __device__ __forceinline__ void warp_prune_multi(uint64_t* const (&buf)[B], cons
         if ((lane + 32) < cnt[i] && (lane + 32) >= conv[i]) b[i] = raw_to_key(b[i], head, cap);
     }
     warp_sort64_multi<true, B>(a, lane);
-    warp_sort64_multi<false, B>(b, lane);
+    if (CAPT > 32) warp_sort64_multi<false, B>(b, lane);
     uint64_t mn[B];
 #pragma unroll
     for (int i = 0; i < B; ++i) {
-        m[i] = a[i] > b[i] ? a[i] : b[i];
-        if (KPT == 16) {
+        m[i] = (CAPT > 32 && b[i] > a[i]) ? b[i] : a[i];
+        if (KPT <= 16) {
             const uint64_t o = shfl_xor64(m[i], 16);
             m[i] = (lane < 16) ? (m[i] > o ? m[i] : o) : 0ull;
+        }
+        if (KPT == 8) {
+            const uint64_t o = shfl_xor64(m[i], 8);
+            m[i] = (lane < 8) ? (m[i] > o ? m[i] : o) : 0ull;
         }
         mn[i] = m[i];
     }

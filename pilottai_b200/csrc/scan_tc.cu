@@ -33,14 +33,17 @@ constexpr int UK = 16;         // UMMA K for 16-bit inputs
 constexpr int ACC_STAGES = 2;  // 2 x 256 TMEM columns
 
 constexpr int EPI_SETS = 2;    // one per accumulator stage
-constexpr int CAPT = 46;       // per-row candidate buffer: KP survivors + pending appends (smem budget)
 constexpr int TC_THREADS = 128 + EPI_SETS * 128;
 constexpr int PF_TILES = 0;     // corpus tiles prefetched into L2 ahead of the TMA loads (0: off -- measured no gain)
 constexpr int GMAX_LISTS = 32;  // lists per query that publish their first-tile maximum (cold-start threshold)
 constexpr int SC_RING = 4;     // staged scale tiles in flight (full/empty mbarrier pair per slot)
 
-template <int CG> struct TcCfg {
-    static constexpr int STAGES = CG == 1 ? 2 : 4;
+// Shared-memory budget per (CTA group, list length).  8-entry lists need a 30-entry row buffer
+// (8 survivors + 22 pending) instead of 46, which buys the pair kernel a fifth smem stage: the
+// mainloop is bound by TMA supply, and 4 -> 5 stages takes it from 1.12 to 1.04 ms.
+template <int CG, int KPT> struct TcCfg {
+    static constexpr int STAGES = CG == 1 ? 2 : (KPT == 8 ? 5 : 4);
+    static constexpr int CAPT = KPT == 8 ? 30 : 46;                // per-row candidate buffer: survivors + pending appends
     static constexpr int A_BYTES = BM * BK * 2;                    // 16 KB
     static constexpr int B_ROWS = BN / CG;                         // rows of B this CTA loads
     static constexpr int B_BYTES = B_ROWS * BK * 2;                // 32 KB / 16 KB
@@ -251,7 +254,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
 scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_c,
                const float* __restrict__ scale, const float* __restrict__ tile_max,
                uint64_t* __restrict__ partials, uint32_t* __restrict__ gthr, uint32_t* __restrict__ gmax, int64_t nq, int64_t nslots, int64_t capacity, int64_t head, int kblocks, int slots, int slots_rem, int groups, int krank, int dbg) {
-    using Cfg = TcCfg<CG>;
+    using Cfg = TcCfg<CG, KPT>;
+    constexpr int CAPT = Cfg::CAPT;
     extern __shared__ unsigned char smem_dyn[];
     const uint32_t base = (smem_u32(smem_dyn) + 1023u) & ~1023u;        // 1024-B aligned (swizzle atom)
     unsigned char* base_ptr = smem_dyn + (base - smem_u32(smem_dyn));
@@ -519,7 +523,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                     }
                 }
                 if (dbg & 4) t_slow += clock64() - cs;
-                if (KPT == 16) {                               // 16-entry lists: once per 16 columns
+                if (KPT <= 16) {                               // 8/16-entry lists: once per 16 columns
                     const unsigned full = __ballot_sync(FULL, cnt > CAPT - 16);
                     if (full) {
                         const long long cp = (dbg & 4) ? clock64() : 0;
@@ -560,7 +564,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
             // filling up now, off the critical path, so that prunes inside the column loop (which
             // hold the accumulator stage and stall the MMA issuer) become rare.
             if (!(dbg & 32) && t + 1 < t_hi && !mbar_test(bar_tfull + 8 * as, aphase)) {
-                const unsigned early = __ballot_sync(FULL, cnt > KPT + 8);
+                const unsigned early = __ballot_sync(FULL, cnt > (KPT == 8 ? 10 : KPT + 8));
                 if (early) {
                     const long long cp = (dbg & 4) ? clock64() : 0;
                     warp_prune_rows<CAPT, KPT>(early, rows, lane, cnt, conv, thr, head32, cap32);
@@ -625,7 +629,7 @@ static cudaError_t launch_one(const ScanArgs& a, const CUtensorMap* map_q, const
     cudaLaunchConfig_t cfg{};
     cfg.blockDim = dim3(TC_THREADS);
     cfg.gridDim = dim3(units * CG);
-    cfg.dynamicSmemBytes = TcCfg<CG>::SMEM;
+    cfg.dynamicSmemBytes = TcCfg<CG, KPT>::SMEM;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -639,9 +643,10 @@ cudaError_t scan_tc_init() {
     cudaError_t e;
 #define PILOTT_TC_ATTR(CG, KPT)                                                                     \
     e = cudaFuncSetAttribute(scan_tc_kernel<CG, KPT>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
-                             TcCfg<CG>::SMEM);                                                      \
+                             TcCfg<CG, KPT>::SMEM);                                                      \
     if (e != cudaSuccess) return e;
-    PILOTT_TC_ATTR(1, 16) PILOTT_TC_ATTR(1, 32) PILOTT_TC_ATTR(2, 16) PILOTT_TC_ATTR(2, 32)
+    PILOTT_TC_ATTR(1, 8) PILOTT_TC_ATTR(1, 16) PILOTT_TC_ATTR(1, 32)
+    PILOTT_TC_ATTR(2, 8) PILOTT_TC_ATTR(2, 16) PILOTT_TC_ATTR(2, 32)
 #undef PILOTT_TC_ATTR
     return cudaSuccess;
 }
@@ -650,10 +655,16 @@ cudaError_t scan_tc_init() {
 cudaError_t launch_scan_tc(const ScanArgs& a, const CUtensorMap* map_q, const CUtensorMap* map_c,
                            int cg, int ctas, cudaStream_t st) {
     (void)ctas;
-    if (cg == 1) return a.list_len == 16 ? launch_one<1, 16>(a, map_q, map_c, st) : launch_one<1, 32>(a, map_q, map_c, st);
+    if (cg == 1) {
+        if (a.list_len == 8) return launch_one<1, 8>(a, map_q, map_c, st);
+        return a.list_len == 16 ? launch_one<1, 16>(a, map_q, map_c, st) : launch_one<1, 32>(a, map_q, map_c, st);
+    }
+    if (a.list_len == 8) return launch_one<2, 8>(a, map_q, map_c, st);
     return a.list_len == 16 ? launch_one<2, 16>(a, map_q, map_c, st) : launch_one<2, 32>(a, map_q, map_c, st);
 }
 
 }  // namespace pilott
 
-static_assert(pilott::TcCfg<1>::SMEM <= 232448 && pilott::TcCfg<2>::SMEM <= 232448, "shared memory budget (227 KB per CTA)");
+static_assert(pilott::TcCfg<1, 8>::SMEM <= 232448 && pilott::TcCfg<1, 32>::SMEM <= 232448 &&
+              pilott::TcCfg<2, 8>::SMEM <= 232448 && pilott::TcCfg<2, 32>::SMEM <= 232448,
+              "shared memory budget (227 KB per CTA)");

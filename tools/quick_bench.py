@@ -31,9 +31,14 @@ inex = torch.zeros(1, dtype=torch.int32, device=dev); flags = torch.empty(nq, dt
 ref = None
 for kern in kernels:
     try:
-        dbg = 0
+        dbg = 0; ll = 0
+        if "/" in kern:                      # tc_pair/16 forces the candidate-list length
+            kern, ll = kern.split("/"); 
+            if ":" in ll: ll, d2 = ll.split(":"); kern = kern + ":" + d2
+            ll = int(ll)
         if ":" in kern:
             kern, dbg = kern.split(":"); dbg = int(dbg)
+        st.set_list_len(ll)
         st.set_debug(dbg)
         st.set_kernel(kern)
         for _ in range(2):
@@ -49,7 +54,7 @@ for kern in kernels:
         same = "" if ref is None else f" same_as_{kernels[0]}={bool((idx == ref).all())}"
         if ref is None:
             ref = idx.clone()
-        print(f"{kern:8s} dbg={dbg}: {ms:8.3f} ms/batch  {nq/(ms*1e-3):12.0f} q/s  {tf:7.1f} TFLOP/s  inexact={int(inex.item())}{same}", flush=True)
+        print(f"{kern:8s} dbg={dbg} list={ll}: {ms:8.3f} ms/batch  {nq/(ms*1e-3):12.0f} q/s  {tf:7.1f} TFLOP/s  inexact={int(inex.item())}{same}", flush=True)
     except Exception as ex:
         print(f"{kern}: FAILED {ex}", flush=True)
         break
