@@ -15,23 +15,25 @@
 
 namespace pilott {
 
-template <int W>
+// Shared-memory agent record, in 8-byte words (all lanes read the same record = broadcast):
+//   [0, nw) capability words | [nw, 2nw) specialization words | t4 | flags | s12[0..2] | pad to even
+// so that for one-word vocabularies (caps, spec) and (t4, flags) each come with one 16-byte load.
+__host__ __device__ inline int route_record_words(int nw) { return (2 * nw + 5 + 1) & ~1; }
+
+template <int W, int MODE>
 __global__ void __launch_bounds__(256)
 route_kernel(const uint64_t* __restrict__ task_req, const uint64_t* __restrict__ task_tags,
              const int32_t* __restrict__ task_type, const uint8_t* __restrict__ task_flags, int64_t nt,
              const uint64_t* __restrict__ agent_caps, const uint64_t* __restrict__ agent_spec,
              const uint8_t* __restrict__ agent_flags, const double* __restrict__ agent_s12,
              const double* __restrict__ agent_t4, int na, int words, const double* __restrict__ spec_u,
-             int max_tags, int mode, int chunk, int32_t* __restrict__ out_agent,
+             int max_tags, int chunk, int32_t* __restrict__ out_agent,
              double* __restrict__ out_score) {
     extern __shared__ __align__(16) unsigned char sm_raw[];
     const int nw = W > 0 ? W : words;
-    double* s_s12 = reinterpret_cast<double*>(sm_raw);                 // [chunk][3]
-    double* s_t4 = s_s12 + (size_t)chunk * 3;                          // [chunk]
-    double* s_u = s_t4 + chunk;                                        // [2*(max_tags+1)]
-    uint64_t* s_caps = reinterpret_cast<uint64_t*>(s_u + 2 * (max_tags + 1));   // [chunk][nw]
-    uint64_t* s_spec = s_caps + (size_t)chunk * nw;                    // [chunk][nw]
-    uint8_t* s_flags = reinterpret_cast<uint8_t*>(s_spec + (size_t)chunk * nw);  // [chunk]
+    const int RW = route_record_words(nw);
+    uint64_t* s_rec = reinterpret_cast<uint64_t*>(sm_raw);             // [chunk][RW]
+    double* s_u = reinterpret_cast<double*>(s_rec + (size_t)chunk * RW);   // [2*(max_tags+1)]
 
     for (int i = threadIdx.x; i < 2 * (max_tags + 1); i += blockDim.x) s_u[i] = spec_u[i];
 
@@ -49,55 +51,100 @@ route_kernel(const uint64_t* __restrict__ task_req, const uint64_t* __restrict__
         }
     }
     const bool has_req_key = tf & 1, has_type_key = tf & 2, req_unknown = tf & 4;
+    // type membership as one AND: word index + single-bit mask (mask 0 = task names no type)
+    const int tw = type >= 0 ? (type >> 6) : 0;
+    const uint64_t tm = type >= 0 ? (1ull << (type & 63)) : 0ull;
+    // agent.py:551-556 as one mask test: the base score is 0 when the task carries the key and the
+    // agent lacks the attribute (flag bit 1 clear), lacks a required capability, or the task names
+    // a capability no agent knows (bit 2, which no agent flag ever has).  Without the key nothing
+    // is required at all.
+    const uint32_t need = has_req_key ? (2u | (req_unknown ? 4u : 0u)) : 0u;
+    if (W > 0 && !has_req_key) {
+#pragma unroll
+        for (int w = 0; w < (W > 0 ? W : 1); ++w) req[w] = 0ull;
+    }
+    const int u_hi = max_tags + 1;
     double best = 0.0;
     int best_a = -1;
 
     for (int a0 = 0; a0 < na; a0 += chunk) {
         const int nc = min(chunk, na - a0);
         __syncthreads();
-        for (int i = threadIdx.x; i < nc * 3; i += blockDim.x) s_s12[i] = agent_s12[(size_t)a0 * 3 + i];
-        for (int i = threadIdx.x; i < nc; i += blockDim.x) { s_t4[i] = agent_t4[a0 + i]; s_flags[i] = agent_flags[a0 + i]; }
-        for (int i = threadIdx.x; i < nc * nw; i += blockDim.x) {
-            s_caps[i] = agent_caps[(size_t)a0 * nw + i];
-            s_spec[i] = agent_spec[(size_t)a0 * nw + i];
+        for (int i = threadIdx.x; i < nc; i += blockDim.x) {
+            uint64_t* r = s_rec + (size_t)i * RW;
+            for (int w = 0; w < nw; ++w) {
+                r[w] = agent_caps[(size_t)(a0 + i) * nw + w];
+                r[nw + w] = agent_spec[(size_t)(a0 + i) * nw + w];
+            }
+            r[2 * nw] = (uint64_t)__double_as_longlong(agent_t4[a0 + i]);
+            r[2 * nw + 1] = agent_flags[a0 + i] & 3u;
+            r[2 * nw + 2] = (uint64_t)__double_as_longlong(agent_s12[(size_t)(a0 + i) * 3]);
+            r[2 * nw + 3] = (uint64_t)__double_as_longlong(agent_s12[(size_t)(a0 + i) * 3 + 1]);
+            r[2 * nw + 4] = (uint64_t)__double_as_longlong(agent_s12[(size_t)(a0 + i) * 3 + 2]);
         }
         __syncthreads();
         if (!live) continue;
-        for (int a = 0; a < nc; ++a) {
-            const uint8_t f = s_flags[a];
-            if (!(f & 1)) continue;                                    // not viable / skipped
-            bool missing;
+        // score of agent a of this chunk; false = agent skipped for this task.  Branch-free.
+        auto eval = [&](const int a, double& sc) -> bool {
+            const uint64_t* r = s_rec + (size_t)a * RW;
+            uint64_t miss = 0, tsel = 0;
             int tagc = 0;
-            bool tbit = false;
-            if (W > 0) {
-                uint64_t miss = 0;
-#pragma unroll
-                for (int w = 0; w < (W > 0 ? W : 1); ++w) {
-                    miss |= req[w] & ~s_caps[a * nw + w];
-                    tagc += __popcll(tags[w] & s_spec[a * nw + w]);
-                }
-                missing = miss != 0;
-                if (type >= 0) tbit = (s_spec[a * nw + (type >> 6)] >> (type & 63)) & 1;
+            if (W == 1) {
+                const ulonglong2 cs = *reinterpret_cast<const ulonglong2*>(r);          // caps, spec
+                miss = req[0] & ~cs.x;
+                tagc = __popcll(tags[0] & cs.y);
+                tsel = cs.y & tm;
+            } else if (W == 2) {
+                const ulonglong2 c = *reinterpret_cast<const ulonglong2*>(r);
+                const ulonglong2 sp = *reinterpret_cast<const ulonglong2*>(r + 2);
+                miss = (req[0] & ~c.x) | (req[1] & ~c.y);
+                tagc = __popcll(tags[0] & sp.x) + __popcll(tags[1] & sp.y);
+                tsel = (tw ? sp.y : sp.x) & tm;
             } else {
-                uint64_t miss = 0;
                 for (int w = 0; w < nw; ++w) {
-                    miss |= task_req[t * nw + w] & ~s_caps[a * nw + w];
-                    tagc += __popcll(task_tags[t * nw + w] & s_spec[a * nw + w]);
+                    miss |= task_req[t * nw + w] & ~r[w];
+                    tagc += __popcll(task_tags[t * nw + w] & r[nw + w]);
                 }
-                missing = miss != 0;
-                if (type >= 0) tbit = (s_spec[a * nw + (type >> 6)] >> (type & 63)) & 1;
+                tsel = r[nw + tw] & tm;
+                if (!has_req_key) miss = 0;
             }
-            // agent.py:551-556: key present and (attribute missing -> exception -> 0.0, or caps missing)
-            const bool zero_base = has_req_key && (!(f & 2) || missing || req_unknown);
-            const int sel = zero_base ? 0 : ((has_type_key && tbit) ? 2 : 1);   // agent.py:562-564
-            double sc = s_s12[a * 3 + sel];
-            if (mode == 0) {
-                const double u = s_u[(tbit ? (max_tags + 1) : 0) + tagc];      // router.py:116-126
-                sc = __dadd_rn(__dadd_rn(sc, u), s_t4[a]);
+            const ulonglong2 tfl = *reinterpret_cast<const ulonglong2*>(r + 2 * nw);    // t4, flags
+            const uint32_t f = (uint32_t)tfl.y;
+            const bool tbit = tsel != 0;
+            const bool zero_base = ((uint32_t)miss | (uint32_t)(miss >> 32) | (need & ~f)) != 0u;
+            const int sel = zero_base ? 0 : ((has_type_key & tbit) ? 2 : 1);           // agent.py:562-564
+            sc = __longlong_as_double((long long)r[2 * nw + 2 + sel]);
+            if (MODE == 0) {
+                const double u = s_u[(tbit ? u_hi : 0) + tagc];                        // router.py:116-126
+                sc = __dadd_rn(__dadd_rn(sc, u), __longlong_as_double((long long)tfl.x));
             }
-            if (mode == 2 && !(sc > 0.0)) continue;                    // task_delegator.py:75
-            if (best_a < 0 || sc > best) { best = sc; best_a = a0 + a; }
+            bool ok = f & 1;                                           // not viable / skipped
+            if (MODE == 2) ok &= sc > 0.0;                             // task_delegator.py:75
+            return ok;
+        };
+        // Four agents per trip: their shared-memory loads and fp64 additions are independent, so the
+        // chains overlap; the first-max update then runs in table order.
+#define ROUTE_TAKE(K, S, A)                                              \
+        {                                                                \
+            const bool upd = (K) & ((best_a < 0) | ((S) > best));        \
+            best = upd ? (S) : best;                                     \
+            best_a = upd ? (A) : best_a;                                 \
         }
+        int a = 0;
+        for (; a + 4 <= nc; a += 4) {
+            double s0, s1, s2, s3;
+            const bool k0 = eval(a, s0), k1 = eval(a + 1, s1), k2 = eval(a + 2, s2), k3 = eval(a + 3, s3);
+            ROUTE_TAKE(k0, s0, a0 + a)
+            ROUTE_TAKE(k1, s1, a0 + a + 1)
+            ROUTE_TAKE(k2, s2, a0 + a + 2)
+            ROUTE_TAKE(k3, s3, a0 + a + 3)
+        }
+        for (; a < nc; ++a) {
+            double s0;
+            const bool k0 = eval(a, s0);
+            ROUTE_TAKE(k0, s0, a0 + a)
+        }
+#undef ROUTE_TAKE
     }
     if (live) {
         out_agent[t] = best_a;
@@ -113,29 +160,39 @@ cudaError_t launch_route(const uint64_t* task_req, const uint64_t* task_tags,
                          int max_tags, int mode, int32_t* out_agent, double* out_score,
                          cudaStream_t st) {
     if (nt <= 0) return cudaSuccess;
-    const size_t per_agent = 3 * 8 + 8 + 2 * 8 * (size_t)words + 1;
+    const size_t per_agent = 8 * (size_t)route_record_words(words);
     const size_t fixed = 2 * (size_t)(max_tags + 1) * 8 + 64;
-    int chunk = (int)((96 * 1024 - fixed) / per_agent);
-    chunk &= ~7;                                   // keeps the uint64 sub-arrays 8-byte aligned
+    // small chunks: 12 KB per CTA lets 5+ CTAs share an SM, and the kernel lives on hiding the
+    // load -> select -> load -> add chains behind other warps
+    int chunk = (int)((12 * 1024 - fixed) / per_agent);
+    if (chunk < 64) chunk = (int)((96 * 1024 - fixed) / per_agent);      // very wide vocabularies
+    chunk &= ~7;
     if (chunk < 8) return cudaErrorInvalidValue;            // vocabulary too wide for shared memory
     if (chunk > ((na + 7) & ~7)) chunk = (na + 7) & ~7;
     if (chunk < 8) chunk = 8;                               // na == 0: every task gets "no agent"
     const size_t smem = fixed + (size_t)chunk * per_agent;
     const unsigned grid = (unsigned)((nt + 255) / 256);
-#define ROUTE_LAUNCH(WT)                                                                         \
+#define ROUTE_LAUNCH(WT, MD)                                                                     \
     do {                                                                                         \
-        cudaError_t e = cudaFuncSetAttribute(route_kernel<WT>,                                   \
+        cudaError_t e = cudaFuncSetAttribute(route_kernel<WT, MD>,                               \
                                              cudaFuncAttributeMaxDynamicSharedMemorySize,        \
                                              (int)smem);                                         \
         if (e != cudaSuccess) return e;                                                          \
-        route_kernel<WT><<<grid, 256, smem, st>>>(task_req, task_tags, task_type, task_flags, nt, \
-                                                  agent_caps, agent_spec, agent_flags, agent_s12, \
-                                                  agent_t4, na, words, spec_u, max_tags, mode,   \
-                                                  chunk, out_agent, out_score);                  \
+        route_kernel<WT, MD><<<grid, 256, smem, st>>>(task_req, task_tags, task_type, task_flags, \
+                                                      nt, agent_caps, agent_spec, agent_flags,   \
+                                                      agent_s12, agent_t4, na, words, spec_u,    \
+                                                      max_tags, chunk, out_agent, out_score);    \
     } while (0)
-    if (words == 1) ROUTE_LAUNCH(1);
-    else if (words == 2) ROUTE_LAUNCH(2);
-    else ROUTE_LAUNCH(0);
+#define ROUTE_MODES(WT)                                                                          \
+    do {                                                                                         \
+        if (mode == 0) ROUTE_LAUNCH(WT, 0);                                                      \
+        else if (mode == 1) ROUTE_LAUNCH(WT, 1);                                                 \
+        else ROUTE_LAUNCH(WT, 2);                                                                \
+    } while (0)
+    if (words == 1) ROUTE_MODES(1);
+    else if (words == 2) ROUTE_MODES(2);
+    else ROUTE_MODES(0);
+#undef ROUTE_MODES
 #undef ROUTE_LAUNCH
     return cudaGetLastError();
 }
