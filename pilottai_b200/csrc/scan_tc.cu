@@ -395,10 +395,14 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
         uint64_t* rows = bufs + ((size_t)set * BM + quarter * 32) * CAPT;
         uint64_t* mine = bufs + ((size_t)set * BM + row) * CAPT;
         const uint32_t head32 = (uint32_t)head, cap32 = (uint32_t)capacity;
-        float thr = (dbg & 128) ? INFINITY : -INFINITY;   // dbg & 128: fast path only (no candidate ever passes)
-        int cnt = 0, conv = 0;
         const int64_t qrow = q0 + row;
         const bool has_q = qrow < nq;
+        // Padding rows (no query behind them: ragged batches, or the second CTA of a pair when fewer
+        // than 129 queries come in) score 0 everywhere; with an open threshold each of them would
+        // collect and prune candidates all sweep long.  +inf keeps them on the fast path.
+        // dbg & 128: fast path only (no candidate ever passes).
+        float thr = (!has_q || (dbg & 128)) ? INFINITY : -INFINITY;
+        int cnt = 0, conv = 0;
         uint32_t aphase = 0;
         int as = 0;
         // cold-start protocol needs at least `krank` publishing lists for this query (krank = rank of
