@@ -96,14 +96,15 @@ int pilott_mem_append_host(pilott_mem_t* h, const float* x_host, int64_t n,
  * k candidates), out_score [nq,k] fp32 (-inf padding), out_score64 [nq,k] fp64 may be NULL.
  * *out_inexact_dev (device int32, may be NULL) receives how many queries could NOT be
  * proven exact (their gap check failed) and out_flags_dev [nq] (uint8, may be NULL) marks
- * them; re-run those through pilott_mem_search_exact.  1 <= k <= PILOTT_MAX_FUSED_K. */
+ * them; re-run those through pilott_mem_search_refine (or pilott_mem_search_exact).
+ * 1 <= k <= PILOTT_MAX_FUSED_K. */
 int pilott_mem_search(pilott_mem_t* h, const float* q_dev, int64_t nq, int k, int32_t min_prio,
                       uint64_t req_tagmask, int64_t now_us, int64_t* out_idx_dev,
                       float* out_score_dev, double* out_score64_dev, int32_t* out_inexact_dev,
                       uint8_t* out_flags_dev, void* stream);
-/* Host-buffer variant: H2D of the queries, the search, the exact fallback for flagged
- * queries (and for k > PILOTT_MAX_FUSED_K), D2H of the results; synchronous.
- * *n_fallback (may be NULL) = queries that went through the exact path. */
+/* Host-buffer variant: H2D of the queries, the search, the second-chance pass for flagged
+ * queries (brute force for k > PILOTT_MAX_FUSED_K), D2H of the results; synchronous.
+ * *n_fallback (may be NULL) = queries that needed more than the fused pass. */
 int pilott_mem_search_host(pilott_mem_t* h, const float* q_host, int64_t nq, int k,
                            int32_t min_prio, uint64_t req_tagmask, int64_t now_us,
                            int64_t* out_idx_host, float* out_score_host, double* out_score64_host,
@@ -115,6 +116,24 @@ int pilott_mem_search_exact(pilott_mem_t* h, const float* q_dev, int64_t nq, con
                             int64_t nsel, int k, int32_t min_prio, uint64_t req_tagmask,
                             int64_t now_us, int64_t* out_idx_dev, float* out_score_dev,
                             double* out_score64_dev, void* stream);
+
+/* Second chance for the queries pilott_mem_search flagged (no counterpart in the reference; it is
+ * the fused path's own repair step).  Same selection arguments as pilott_mem_search_exact, same
+ * bit-identical results, but instead of scoring every row it re-runs the tensor-core scan over the
+ * flagged queries only, with ONE fixed threshold per query: out_idx_dev / out_score64_dev must still
+ * hold what pilott_mem_search wrote for these queries (k rows with exact fp64 scores; the k-th is a
+ * lower bound of the true k-th best), so every row that can belong to the true top-k has an
+ * approximate score above (bound - error margin) and is collected, re-scored by the stated rule and
+ * ranked.  Cost: about one scan of the corpus for up to 256 flagged queries, whatever made them
+ * ambiguous (bursts of near-duplicate rows, exact ties wider than a candidate list).  Queries with
+ * more than 1024 rows inside the margin, k > PILOTT_MAX_FUSED_K, out_score64_dev == NULL or
+ * query_ids_dev == NULL fall through to the brute-force path; *n_bruteforce (host, may be NULL)
+ * says how many did.  The filters must be the ones the flagged search used.  Synchronises `stream`
+ * before returning (it reads an overflow counter). */
+int pilott_mem_search_refine(pilott_mem_t* h, const float* q_dev, int64_t nq, const int32_t* query_ids_dev,
+                             int64_t nsel, int k, int32_t min_prio, uint64_t req_tagmask,
+                             int64_t now_us, int64_t* out_idx_dev, float* out_score_dev,
+                             double* out_score64_dev, int32_t* n_bruteforce, void* stream);
 
 /* Same search as pilott_mem_search_exact, same arguments and bit-identical results, but the
  * call allocates nothing.  It has no counterpart in the reference.

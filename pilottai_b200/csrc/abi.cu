@@ -125,7 +125,7 @@ struct pilott_mem {
     int64_t* expires = nullptr;
     float* scale = nullptr;
     float* tile_max = nullptr;
-    DevBuf qbuf, partials, gthr, exact_scratch, stage_dev, result_dev, misc_dev;
+    DevBuf qbuf, partials, gthr, exact_scratch, stage_dev, result_dev, misc_dev, refine, result_ids;
     HostBuf stage_host;
     cudaStream_t own_stream = nullptr;
     CUtensorMap map_c;
@@ -134,6 +134,8 @@ struct pilott_mem {
     int opt_ctas = 0;
     int opt_dbg = 0;
     int opt_list_len = 0;   // 0 auto, 8, 16, 32
+    int auto_min_list = 8;  // floor of the automatic list length: raised when searches keep flagging queries
+    int64_t searches_since_refine = 0;
     int64_t seq_mul = 1, seq_add = 0;   // reported index = seq * seq_mul + seq_add (row-sharded stores)
     bool profile = false;   // record CUDA events around the scan kernel
     std::vector<cudaEvent_t> ev;        // pairs: [2i] before, [2i+1] after
@@ -244,6 +246,11 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
         const bool lists8 = cg == 2 && k <= 10 && nlists >= 16;
         if (h->opt_list_len == 8 || h->opt_list_len == 16 || h->opt_list_len == 32) a.list_len = h->opt_list_len;
         else a.list_len = lists8 ? 8 : (lists16 ? 16 : 32);
+        // Bursty corpora (runs of near-duplicate rows stored side by side) overflow short lists and
+        // send queries to the second-chance pass; after such a batch the floor goes up (refine_core),
+        // after 512 searches without one it comes back down a step.
+        if (h->opt_list_len == 0 && a.list_len < h->auto_min_list) a.list_len = h->auto_min_list;
+        if (++h->searches_since_refine > 512 && h->auto_min_list > 8) { h->auto_min_list /= 2; h->searches_since_refine = 0; }
         lists = (a.slots + (a.slots_rem > 0 ? 1 : 0)) * pilott::scan_tc_lists_per_slot();
         f.rows_per_group = pilott::scan_tc_rows_per_group(cg);
         f.lists_base = a.slots * pilott::scan_tc_lists_per_slot();
@@ -326,6 +333,90 @@ int exact_core(pilott_mem* h, const float* q_dev, int64_t nq, const int32_t* qid
     return PILOTT_OK;
 }
 
+// Second chance for the queries a fused search flagged (see finish.cu): dense block of the
+// flagged queries -> COLLECT scan with one fixed threshold per query -> exact re-score and rank
+// of the collected rows.  out_idx / out_score64 hold the fused results on entry (their k-th exact
+// score is the lower bound the thresholds come from) and the exact results on return.  Queries
+// with more than REFINE_CAP rows inside the error margin, and every case this pass does not
+// cover (k > 32, no fp64 scores, pair kernel not selectable), go to the brute-force path.
+// Synchronises the stream (it has to read the overflow counter).
+constexpr int REFINE_CAP = 1024;
+
+int refine_core(pilott_mem* h, const float* q_dev, int64_t nq, const int32_t* qids, int64_t nsel, int k,
+                int32_t min_prio, uint64_t req, int64_t now_us, int64_t* out_idx, float* out_score,
+                double* out_score64, int32_t* n_brute, cudaStream_t st) {
+    if (n_brute) *n_brute = 0;
+    if (nq <= 0 || (qids && nsel <= 0)) return PILOTT_OK;
+    if (k < 1) return fail(PILOTT_EINVAL, "k must be >= 1");
+    if (!qids || !out_score64 || k > PILOTT_MAX_FUSED_K || pick_kernel(h) != 3 || h->count == 0) {
+        if (n_brute) *n_brute = (int32_t)(qids ? nsel : nq);
+        return exact_core(h, q_dev, nq, qids, nsel, k, min_prio, req, now_us, out_idx, out_score, out_score64, st);
+    }
+    // a batch that flags more than ~1.5 % of its queries raises the automatic list length
+    if (nsel * 64 > nq && h->auto_min_list < 32) h->auto_min_list *= 2;
+    h->searches_since_refine = 0;
+
+    const int64_t nsel_pad = round_up(nsel, 256);
+    int rc = h->qbuf.ensure((size_t)round_up(nq, 256) * h->ld * 2);
+    if (rc) return rc;
+    const size_t qb2_b = (size_t)nsel_pad * h->ld * 2, w_b = (size_t)nsel_pad * 4;
+    const size_t cand_b = (size_t)nsel * REFINE_CAP * 4, ovf_b = (size_t)round_up(nsel, 8);
+    rc = h->refine.ensure(qb2_b + 2 * w_b + cand_b + ovf_b + 8);
+    if (rc) return rc;
+    char* base = (char*)h->refine.p;
+    void* qb2 = base;
+    uint32_t* thr_bits = (uint32_t*)(base + qb2_b);
+    uint32_t* cnt = (uint32_t*)(base + qb2_b + w_b);
+    uint32_t* cand = (uint32_t*)(base + qb2_b + 2 * w_b);
+    uint8_t* ovf = (uint8_t*)(base + qb2_b + 2 * w_b + cand_b);
+    int32_t* n_ovf = (int32_t*)(base + qb2_b + 2 * w_b + cand_b + ovf_b);
+
+    // query conversion + scale pre-pass for THESE filters (the scan reads h->scale / h->tile_max)
+    CK(pilott::launch_prepare(q_dev, nq, h->dim, h->ld, h->qbuf.p, h->inv_norm, h->prio, h->tagmask, h->expires,
+                              h->count, h->capacity, h->cap_pad, min_prio, req, now_us, h->scale, h->tile_max,
+                              nullptr, 0, nullptr, st));
+    const double err = h->ld * 2.4e-7 > 1e-4 ? h->ld * 2.4e-7 : 1e-4;       // same bound as the gap check
+    CK(pilott::launch_refine_prepare(h->qbuf.p, qids, nsel, nsel_pad, h->ld, out_idx, out_score64, k, err, qb2,
+                                     thr_bits, cnt, n_ovf, st));
+    pilott::ScanArgs a{};
+    a.qb = qb2; a.vec = h->vec; a.scale = h->scale; a.tile_max = h->tile_max; a.nq = nsel;
+    a.nslots = h->count; a.capacity = h->capacity; a.head = h->head; a.ld = h->ld;
+    a.partials = (uint64_t*)cand; a.gthr = thr_bits; a.gmax = cnt; a.collect_cap = REFINE_CAP;
+    a.list_len = 8; a.krank = 16; a.dbg = 0;
+    const int ctas = h->opt_ctas > 0 ? h->opt_ctas : h->num_sms;
+    a.slots = pilott::scan_tc_slots(nsel, h->count, 2, ctas, &a.slots_rem);
+    CUtensorMap map_q, map_c;
+    rc = encode_map(&map_q, qb2, nsel_pad, h->ld, 128);
+    if (rc) return rc;
+    rc = encode_map(&map_c, h->vec, h->capacity, h->ld, 128);
+    if (rc) return rc;
+    CK(pilott::launch_scan_tc(a, &map_q, &map_c, 2, ctas, st));
+    CK(pilott::launch_refine_finish(cand, cnt, REFINE_CAP, qb2, h->vec, h->ld, qids, nsel, h->capacity, h->head,
+                                    h->total - h->count, h->seq_mul, h->seq_add, k, out_idx, out_score, out_score64,
+                                    ovf, n_ovf, st));
+    h->launches += 4;
+    int32_t novf = 0;
+    CK(cudaMemcpyAsync(&novf, n_ovf, 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (novf > 0) {
+        // more near-ties than the candidate array holds: those queries go through the brute-force path
+        std::vector<uint8_t> fl((size_t)nsel);
+        std::vector<int32_t> ids((size_t)nsel), over;
+        CK(cudaMemcpyAsync(fl.data(), ovf, (size_t)nsel, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(ids.data(), qids, (size_t)nsel * 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        for (int64_t i = 0; i < nsel; ++i) if (fl[i]) over.push_back(ids[i]);
+        rc = h->misc_dev.ensure(over.size() * 4);
+        if (rc) return rc;
+        CK(cudaMemcpyAsync(h->misc_dev.p, over.data(), over.size() * 4, cudaMemcpyHostToDevice, st));
+        CK(cudaStreamSynchronize(st));
+        if (n_brute) *n_brute = (int32_t)over.size();
+        return exact_core(h, q_dev, nq, (const int32_t*)h->misc_dev.p, (int64_t)over.size(), k, min_prio, req, now_us,
+                          out_idx, out_score, out_score64, st);
+    }
+    return PILOTT_OK;
+}
+
 }  // namespace
 
 extern "C" int pilott_kp(void) { return 32; }
@@ -372,7 +463,8 @@ int pilott_mem_destroy(pilott_mem_t* h) {
     cudaDeviceSynchronize();
     free_columns(h);
     h->qbuf.release(); h->partials.release(); h->gthr.release(); h->exact_scratch.release(); h->stage_dev.release();
-    h->result_dev.release(); h->misc_dev.release(); h->stage_host.release();
+    h->result_dev.release(); h->misc_dev.release(); h->refine.release(); h->result_ids.release();
+    h->stage_host.release();
     for (cudaEvent_t e : h->ev) cudaEventDestroy(e);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     delete h;
@@ -524,6 +616,18 @@ int pilott_mem_search_exact(pilott_mem_t* h, const float* q_dev, int64_t nq, con
                       out_score_dev, out_score64_dev, (cudaStream_t)stream);
 }
 
+int pilott_mem_search_refine(pilott_mem_t* h, const float* q_dev, int64_t nq, const int32_t* query_ids_dev,
+                             int64_t nsel, int k, int32_t min_prio, uint64_t req_tagmask, int64_t now_us,
+                             int64_t* out_idx_dev, float* out_score_dev, double* out_score64_dev,
+                             int32_t* n_bruteforce, void* stream) {
+    if (!h) return fail(PILOTT_EINVAL, "handle is NULL");
+    if (nq < 0) return fail(PILOTT_EINVAL, "nq is negative");
+    if (nq > 0 && (!q_dev || !out_idx_dev || !out_score_dev)) return fail(PILOTT_EINVAL, "NULL query or output pointer");
+    DeviceGuard g(h->device);
+    return refine_core(h, q_dev, nq, query_ids_dev, nsel, k, min_prio, req_tagmask, now_us, out_idx_dev,
+                       out_score_dev, out_score64_dev, n_bruteforce, (cudaStream_t)stream);
+}
+
 int pilott_mem_search_host(pilott_mem_t* h, const float* q_host, int64_t nq, int k, int32_t min_prio,
                            uint64_t req_tagmask, int64_t now_us, int64_t* out_idx_host,
                            float* out_score_host, double* out_score64_host, int32_t* n_fallback) {
@@ -571,15 +675,16 @@ int pilott_mem_search_host(pilott_mem_t* h, const float* q_host, int64_t nq, int
     CK(cudaMemcpyAsync(rh, rd, rtot, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     if (fused && *(int32_t*)(rh + off_c) > 0) {
-        // exact fallback for the queries whose gap check failed
+        // second-chance pass (brute force behind it) for the queries whose gap check failed
         std::vector<int32_t> ids;
         for (int64_t i = 0; i < nq; ++i) if (((uint8_t*)(rh + off_f))[i]) ids.push_back((int32_t)i);
-        rc = h->misc_dev.ensure(ids.size() * 4);
+        // (own buffer: refine_core uses misc_dev for the ids it hands on to the brute-force path)
+        rc = h->result_ids.ensure(ids.size() * 4);
         if (rc) return rc;
-        CK(cudaMemcpyAsync(h->misc_dev.p, ids.data(), ids.size() * 4, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(h->result_ids.p, ids.data(), ids.size() * 4, cudaMemcpyHostToDevice, st));
         CK(cudaStreamSynchronize(st));
-        rc = exact_core(h, qd, nq, (const int32_t*)h->misc_dev.p, (int64_t)ids.size(), k, min_prio, req_tagmask,
-                        now_us, d_idx, d_s, d_s64, st);
+        rc = refine_core(h, qd, nq, (const int32_t*)h->result_ids.p, (int64_t)ids.size(), k, min_prio, req_tagmask,
+                         now_us, d_idx, d_s, d_s64, nullptr, st);
         if (rc) return rc;
         CK(cudaMemcpyAsync(rh, rd, rtot, cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));

@@ -404,6 +404,134 @@ cudaError_t launch_exact(const void* qb, const void* vec, int ld, const int32_t*
 }
 
 // ---------------------------------------------------------------------------------------
+// Second chance for queries the gap check flagged (near-ties wider than a candidate list, bursts
+// of near-duplicate rows).  The fused search already holds k rows with EXACT scores for such a
+// query; the k-th of them, LB, is a lower bound of the true k-th best.  A row can only belong to
+// the true top-k if its exact score is >= LB, hence (same error bound as the gap check) if its
+// approximate score s~ satisfies s~/|q| + err >= LB.  refine_prepare turns that into one fp32
+// threshold per query and packs the flagged queries into a dense query block; the scan kernel in
+// COLLECT mode appends every row reaching the threshold; refine_finish re-scores those rows by
+// the stated rule and ranks them.  A query with more than `cap` such rows is left to the
+// brute-force path (overflow flag).
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+refine_prepare_kernel(const __nv_bfloat16* __restrict__ qb, const int32_t* __restrict__ qids, int64_t nsel,
+                      int64_t nsel_pad, int ld, const int64_t* __restrict__ prior_idx,
+                      const double* __restrict__ prior_s64, int k, double err,
+                      __nv_bfloat16* __restrict__ qb2, uint32_t* __restrict__ thr_bits,
+                      uint32_t* __restrict__ cnt, int32_t* __restrict__ n_overflow) {
+    const int lane = threadIdx.x & 31;
+    const int64_t i = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (i == 0 && lane == 0) *n_overflow = 0;
+    if (i >= nsel_pad) return;
+    uint4* dst = reinterpret_cast<uint4*>(qb2 + i * ld);
+    if (i >= nsel) {                                   // padding row of the dense block
+        for (int c = lane; c < ld / 8; c += 32) dst[c] = make_uint4(0, 0, 0, 0);
+        if (lane == 0) { thr_bits[i] = __float_as_uint(INFINITY); cnt[i] = 0u; }
+        return;
+    }
+    const int64_t q = qids[i];
+    const uint4* src = reinterpret_cast<const uint4*>(qb + q * ld);
+    double n2 = 0.0;                                   // |q|^2 (threshold only: any accurate sum will do)
+    for (int c = lane; c < ld / 8; c += 32) {
+        const uint4 v = src[c];
+        dst[c] = v;
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const double a = (double)__uint_as_float(w[j] << 16), b = (double)__uint_as_float(w[j] & 0xffff0000u);
+            n2 += a * a + b * b;
+        }
+    }
+#pragma unroll
+    for (int j = 16; j > 0; j >>= 1) n2 += shfl_xor_d(n2, j);
+    if (lane == 0) {
+        const bool have = prior_idx[q * k + (k - 1)] >= 0;          // fused search found k rows
+        float t = -INFINITY;
+        if (have) {
+            // (LB - err) * |q|, pushed down past every rounding on the way (1e-6 relative + one ulp)
+            double td = (prior_s64[q * k + (k - 1)] - err) * sqrt(n2);
+            td -= fabs(td) * 1e-6;
+            t = __double2float_rd(td);
+            if (t == t && fabsf(t) < INFINITY)         // one fp32 step further down
+                t = __uint_as_float(t > 0.f ? __float_as_uint(t) - 1u : (t < 0.f ? __float_as_uint(t) + 1u : 0x80000001u));
+            else if (t != t) t = -INFINITY;
+        }
+        thr_bits[i] = __float_as_uint(t);
+        cnt[i] = 0u;
+    }
+}
+
+constexpr int REFINE_THREADS = 256;
+
+__global__ void __launch_bounds__(REFINE_THREADS)
+refine_finish_kernel(const uint32_t* __restrict__ cand, const uint32_t* __restrict__ cnt, int cap,
+                     const __nv_bfloat16* __restrict__ qb2, const __nv_bfloat16* __restrict__ vec, int ld,
+                     const int32_t* __restrict__ qids, int64_t capacity, int64_t head, int64_t base_seq,
+                     int64_t seq_mul, int64_t seq_add, int k, int64_t* __restrict__ out_idx,
+                     float* __restrict__ out_score, double* __restrict__ out_score64,
+                     uint8_t* __restrict__ overflow, int32_t* __restrict__ n_overflow) {
+    extern __shared__ __align__(16) unsigned char sm_raw[];
+    double* s_sc = reinterpret_cast<double*>(sm_raw);                  // [cap]
+    int64_t* s_age = reinterpret_cast<int64_t*>(s_sc + cap);           // [cap]
+    const int64_t sel = blockIdx.x;
+    const int64_t q = qids[sel];
+    const uint32_t c = cnt[sel];
+    if (c > (uint32_t)cap) {                           // too many near-ties: brute force decides
+        if (threadIdx.x == 0) { overflow[sel] = 1; atomicAdd(n_overflow, 1); }
+        return;
+    }
+    if (threadIdx.x == 0) overflow[sel] = 0;
+    const __nv_bfloat16* qrow = qb2 + sel * ld;
+    for (uint32_t i = threadIdx.x; i < c; i += REFINE_THREADS) {
+        const int64_t slot = cand[sel * cap + i];
+        s_sc[i] = exact_cosine(qrow, vec + slot * ld, ld);
+        int64_t age = slot - head;
+        if (age < 0) age += capacity;
+        s_age[i] = age;
+    }
+    for (int j = threadIdx.x; j < k; j += REFINE_THREADS) {
+        out_idx[q * k + j] = -1;
+        out_score[q * k + j] = -INFINITY;
+        if (out_score64) out_score64[q * k + j] = -INFINITY;
+    }
+    __syncthreads();
+    // rank counting: ages are unique, so (score, age) pairs are and every rank is taken once
+    for (uint32_t i = threadIdx.x; i < c; i += REFINE_THREADS) {
+        const double ms = s_sc[i];
+        const int64_t ma = s_age[i];
+        int rank = 0;
+        for (uint32_t j = 0; j < c; ++j) rank += ranks_before(s_sc[j], s_age[j], ms, ma) ? 1 : 0;
+        if (rank < k) {
+            out_idx[q * k + rank] = (base_seq + ma) * seq_mul + seq_add;
+            out_score[q * k + rank] = (float)ms;
+            if (out_score64) out_score64[q * k + rank] = ms;
+        }
+    }
+}
+
+cudaError_t launch_refine_prepare(const void* qb, const int32_t* qids, int64_t nsel, int64_t nsel_pad, int ld,
+                                  const int64_t* prior_idx, const double* prior_s64, int k, double err, void* qb2,
+                                  uint32_t* thr_bits, uint32_t* cnt, int32_t* n_overflow, cudaStream_t st) {
+    const unsigned grid = (unsigned)((nsel_pad + 3) / 4);
+    refine_prepare_kernel<<<grid, 128, 0, st>>>((const __nv_bfloat16*)qb, qids, nsel, nsel_pad, ld, prior_idx, prior_s64,
+                                                k, err, (__nv_bfloat16*)qb2, thr_bits, cnt, n_overflow);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_refine_finish(const uint32_t* cand, const uint32_t* cnt, int cap, const void* qb2, const void* vec,
+                                 int ld, const int32_t* qids, int64_t nsel, int64_t capacity, int64_t head,
+                                 int64_t base_seq, int64_t seq_mul, int64_t seq_add, int k, int64_t* out_idx,
+                                 float* out_score, double* out_score64, uint8_t* overflow, int32_t* n_overflow,
+                                 cudaStream_t st) {
+    if (nsel <= 0) return cudaSuccess;
+    refine_finish_kernel<<<(unsigned)nsel, REFINE_THREADS, (size_t)cap * 16, st>>>(
+        cand, cnt, cap, (const __nv_bfloat16*)qb2, (const __nv_bfloat16*)vec, ld, qids, capacity, head, base_seq,
+        seq_mul, seq_add, k, out_idx, out_score, out_score64, overflow, n_overflow);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------
 // Multi-GPU merge: [shards, nq, k] exact (score, idx) lists -> global top-k per query by
 // rank counting (shards*k <= 256 candidates; pairs are unique because idx is).
 // ---------------------------------------------------------------------------------------

@@ -24,6 +24,8 @@ struct ScanArgs {
     int list_len;            // candidates per list the scan writes (16 or 32)
     int krank;               // rank of the first-tile list maxima used as cold-start threshold (16 or 32)
     int dbg;                 // developer switches for the tcgen05 kernel (0 in production)
+    int collect_cap;         // > 0: second-chance pass (pair kernel): partials = uint32 [nq][collect_cap] ring slots,
+                             // gthr = float-bit thresholds [nq], gmax = uint32 counters [nq]
 };
 
 // generic CUDA-core scan (any shape).  Returns slots used via args.slots (caller sets).
@@ -67,6 +69,17 @@ struct FinishArgs {
     uint8_t* flags; int32_t* inexact;
 };
 cudaError_t launch_finish(const FinishArgs& a, cudaStream_t st);
+
+
+// second-chance pass for flagged queries (finish.cu); the COLLECT scan runs between the two
+cudaError_t launch_refine_prepare(const void* qb, const int32_t* qids, int64_t nsel, int64_t nsel_pad, int ld,
+                                  const int64_t* prior_idx, const double* prior_s64, int k, double err, void* qb2,
+                                  uint32_t* thr_bits, uint32_t* cnt, int32_t* n_overflow, cudaStream_t st);
+cudaError_t launch_refine_finish(const uint32_t* cand, const uint32_t* cnt, int cap, const void* qb2, const void* vec,
+                                 int ld, const int32_t* qids, int64_t nsel, int64_t capacity, int64_t head,
+                                 int64_t base_seq, int64_t seq_mul, int64_t seq_add, int k, int64_t* out_idx,
+                                 float* out_score, double* out_score64, uint8_t* overflow, int32_t* n_overflow,
+                                 cudaStream_t st);
 
 cudaError_t launch_exact(const void* qb, const void* vec, int ld, const int32_t* prio,
                          const uint64_t* tagmask, const int64_t* expires, int64_t nslots,

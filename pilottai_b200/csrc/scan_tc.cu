@@ -249,7 +249,11 @@ __device__ __forceinline__ uint32_t kth_largest_of_32(uint32_t (&v)[32], int kth
 // ---- the kernel ------------------------------------------------------------------------
 // Grid: `units` work units (CTAs for CG=1, CTA pairs for CG=2).  Unit u serves query group
 // u % groups (BM*CG query rows) and slot u / groups of that group.
-template <int CG, int KPT>
+// COLLECT = true is the second-chance pass for queries the gap check flagged: no lists, no
+// pruning -- every row whose approximate score reaches the query's FIXED threshold
+// (thresholds in `gthr` as float bits, one per query row) has its ring slot appended to the
+// query's candidate array (`partials` viewed as uint32 [nq][krank], counters in `gmax`).
+template <int CG, int KPT, bool COLLECT>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_c,
                const float* __restrict__ scale, const float* __restrict__ tile_max,
@@ -402,13 +406,15 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
         // collect and prune candidates all sweep long.  +inf keeps them on the fast path.
         // dbg & 128: fast path only (no candidate ever passes).
         float thr = (!has_q || (dbg & 128)) ? INFINITY : -INFINITY;
+        if (COLLECT && has_q) thr = __uint_as_float(__ldg(gthr + qrow));
+        uint32_t* const cbuf = reinterpret_cast<uint32_t*>(partials) + (has_q ? qrow : 0) * (int64_t)krank;
         int cnt = 0, conv = 0;
         uint32_t aphase = 0;
         int as = 0;
         // cold-start protocol needs at least `krank` publishing lists for this query (krank = rank of
         // the list maxima used as threshold: comfortably below the k results the caller wants)
         const int nlists_q = min(slots_g * EPI_SETS, GMAX_LISTS);
-        const bool cold = nlists_q >= krank && !(dbg & 16);
+        const bool cold = !COLLECT && nlists_q >= krank && !(dbg & 16);
         const int cold_need = max(krank, nlists_q - 4);
         long long w_tfull = 0, t_start = clock64();
         int n_prune = 0, n_slow = 0;
@@ -419,7 +425,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
             const uint32_t n0 = (uint32_t)(t * BN);
             // Any list's KPT-th best score for this query bounds the global top-KPT from below, so
             // all CTAs sweeping the same query share one monotone threshold through gthr[query].
-            const uint32_t g = has_q ? __ldcg(gthr + qrow) : 0u;
+            const uint32_t g = (!COLLECT && has_q) ? __ldcg(gthr + qrow) : 0u;
             const float smax = __ldg(tile_max + t);                 // largest valid scale in this tile
             const int64_t ti = t - t_lo;
             const float* scb = ssc + (ti % SC_RING) * BN;
@@ -428,7 +434,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
             mbar_wait(bar_tfull + 8 * as, aphase);
             if (dbg & 4) w_tfull += clock64() - c0;
             tc_fence_after();
-            if (g > f2ord(thr)) thr = ord2f(g);
+            if (!COLLECT && g > f2ord(thr)) thr = ord2f(g);
             const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
             // ---- cold start (first tile only) -------------------------------------------------
             // With thr = -inf every element of the first tiles is a candidate and every row prunes
@@ -514,8 +520,14 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                         if (dbg & 4) ++n_slow;
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
-                            if (s[4 * g + j] >= thr)
-                                mine[cnt++] = ((uint64_t)f2ord(s[4 * g + j]) << 32) | (n0 + c + 4 * g + j);
+                            if (s[4 * g + j] >= thr) {
+                                if (COLLECT) {
+                                    const uint32_t pos = atomicAdd(gmax + qrow, 1u);
+                                    if (pos < (uint32_t)krank) cbuf[pos] = n0 + c + 4 * g + j;
+                                } else {
+                                    mine[cnt++] = ((uint64_t)f2ord(s[4 * g + j]) << 32) | (n0 + c + 4 * g + j);
+                                }
+                            }
                         }
                     }
                     if (KPT == 32 && (g & 1)) {                // 32-entry lists: fullness check every 8
@@ -581,15 +593,17 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
             printf("[epi cta %d warp %d] total %lld cyc, wait accumulator-full %lld, column loop %lld (slow path %lld in %d groups, prune %lld for %d rows), idle-time prune %lld for %d rows\n",
                    (int)blockIdx.x, warp, clock64() - t_start, w_tfull, t_loop, t_slow, n_slow, t_prune, n_prune, t_early, n_early);
         // flush: final prune of every row (four at a time), write this (slot, set) candidate list
-        warp_prune_all_rows<CAPT, KPT>(rows, lane, cnt, conv, thr, head32, cap32);
-        // every row this list ever dropped scored below its final threshold: finish_kernel's gap check
-        // needs the largest of them per query
-        if (has_q && thr > -INFINITY) atomicMax(gthr + qrow, f2ord(thr));
-        for (int r = 0; r < 32; ++r) {
-            const int c = __shfl_sync(FULL, cnt, r);
-            const int64_t q = q0 + quarter * 32 + r;
-            if (q < nq && lane < KPT)
-                partials[(q * max_lists + slot * EPI_SETS + set) * KPT + lane] = lane < c ? rows[r * CAPT + lane] : 0ull;
+        if (!COLLECT) {
+            warp_prune_all_rows<CAPT, KPT>(rows, lane, cnt, conv, thr, head32, cap32);
+            // every row this list ever dropped scored below its final threshold: finish_kernel's gap
+            // check needs the largest of them per query
+            if (has_q && thr > -INFINITY) atomicMax(gthr + qrow, f2ord(thr));
+            for (int r = 0; r < 32; ++r) {
+                const int c = __shfl_sync(FULL, cnt, r);
+                const int64_t q = q0 + quarter * 32 + r;
+                if (q < nq && lane < KPT)
+                    partials[(q * max_lists + slot * EPI_SETS + set) * KPT + lane] = lane < c ? rows[r * CAPT + lane] : 0ull;
+            }
         }
     }
 
@@ -623,7 +637,7 @@ int scan_tc_slots(int64_t nq, int64_t nslots, int cg, int ctas, int* rem) {
     return (int)s;
 }
 
-template <int CG, int KPT>
+template <int CG, int KPT, bool COLLECT = false>
 static cudaError_t launch_one(const ScanArgs& a, const CUtensorMap* map_q, const CUtensorMap* map_c,
                               cudaStream_t st) {
     const int rows_per_unit = BM * CG;
@@ -639,19 +653,22 @@ static cudaError_t launch_one(const ScanArgs& a, const CUtensorMap* map_q, const
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, scan_tc_kernel<CG, KPT>, *map_q, *map_c, a.scale, a.tile_max, a.partials, a.gthr, a.gmax,
-                              a.nq, a.nslots, a.capacity, a.head, kblocks, a.slots, a.slots_rem, groups, a.krank, a.dbg);
+    return cudaLaunchKernelEx(&cfg, scan_tc_kernel<CG, KPT, COLLECT>, *map_q, *map_c, a.scale, a.tile_max, a.partials, a.gthr, a.gmax,
+                              a.nq, a.nslots, a.capacity, a.head, kblocks, a.slots, a.slots_rem, groups,
+                              COLLECT ? a.collect_cap : a.krank, a.dbg);
 }
 
 cudaError_t scan_tc_init() {
     cudaError_t e;
 #define PILOTT_TC_ATTR(CG, KPT)                                                                     \
-    e = cudaFuncSetAttribute(scan_tc_kernel<CG, KPT>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
+    e = cudaFuncSetAttribute(scan_tc_kernel<CG, KPT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
                              TcCfg<CG, KPT>::SMEM);                                                      \
     if (e != cudaSuccess) return e;
     PILOTT_TC_ATTR(1, 8) PILOTT_TC_ATTR(1, 16) PILOTT_TC_ATTR(1, 32)
     PILOTT_TC_ATTR(2, 8) PILOTT_TC_ATTR(2, 16) PILOTT_TC_ATTR(2, 32)
 #undef PILOTT_TC_ATTR
+    e = cudaFuncSetAttribute(scan_tc_kernel<2, 8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<2, 8>::SMEM);
+    if (e != cudaSuccess) return e;
     return cudaSuccess;
 }
 
@@ -659,6 +676,7 @@ cudaError_t scan_tc_init() {
 cudaError_t launch_scan_tc(const ScanArgs& a, const CUtensorMap* map_q, const CUtensorMap* map_c,
                            int cg, int ctas, cudaStream_t st) {
     (void)ctas;
+    if (a.collect_cap > 0) return launch_one<2, 8, true>(a, map_q, map_c, st);     // pair kernel only
     if (cg == 1) {
         if (a.list_len == 8) return launch_one<1, 8>(a, map_q, map_c, st);
         return a.list_len == 16 ? launch_one<1, 16>(a, map_q, map_c, st) : launch_one<1, 32>(a, map_q, map_c, st);

@@ -64,12 +64,17 @@ class ShardedSemanticStore:
             }
         return self._bufs[key]
 
-    def search_begin(self, q: torch.Tensor, k: int, slot: int = 0, **flt):
+    def search_begin(self, q: torch.Tensor, k: int, slot: int = 0, resolve: bool = False, **flt):
         """Local search + ONE asynchronous all-gather of the packed (index, score) block.
         Returns a ticket for search_end(); with two slots a caller overlaps the exchange of
-        batch i with the local search of batch i+1."""
+        batch i with the local search of batch i+1.  resolve=True reads the local inexact
+        counter (one host sync) and repairs flagged queries before the exchange; with
+        resolve=False the caller checks the counter search_end() returns."""
         b = self._buffers(q.shape[0], k, q.device, slot)
         self.local.search_into(q, k, b["idx"], b["sc"], b["sc64"], b["inexact"], b["flags"], **flt)
+        if resolve and int(b["inexact"].item()):
+            self.local.refine(q, k, b["flags"].nonzero(), (b["idx"], b["sc"], b["sc64"]), **flt)
+            b["inexact"].zero_()
         work = None
         if self.world > 1:
             work = dist.all_gather_into_tensor(b["gathered"], b["mine"], group=self.group, async_op=True)
@@ -85,8 +90,8 @@ class ShardedSemanticStore:
 
     def search(self, q: torch.Tensor, k: int, **flt):
         """q: CUDA fp32 [Q, dim], same on every rank.  Returns (idx, score, score64) on every rank,
-        plus the local inexact counter (callers check it, see SemanticStore.search)."""
-        return self.search_end(self.search_begin(q, k, 0, **flt))
+        plus the local inexact counter (0: flagged queries are repaired locally before the exchange)."""
+        return self.search_end(self.search_begin(q, k, 0, True, **flt))
 
     def close(self):
         self.local.close()

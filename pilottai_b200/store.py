@@ -201,6 +201,31 @@ class SemanticStore:
                                                 self._stream()))
         return idx, sc, sc64
 
+    def refine(self, q, k: int, query_ids, out, min_priority: int = 0, req_tagmask: int = 0, now_us: int = 0) -> int:
+        """Second-chance pass for the queries a fused search flagged (pilott_mem_search_refine):
+        `out` = (idx, score, score64) tensors still holding that search's results, `query_ids` the
+        flagged rows (e.g. flags.nonzero()).  Overwrites those rows of `out` with the exact answer and
+        returns how many queries needed the brute-force path.  Synchronises the stream."""
+        torch = _torch()
+        idx, sc, sc64 = out
+        if sc64 is None:
+            raise ValueError("refine needs the fp64 scores of the fused search (pass sc64)")
+        ids = query_ids.to(device=q.device, dtype=torch.int32).contiguous().view(-1)
+        nb = C.c_int32()
+        check(self._lib.pilott_mem_search_refine(self._h, ptr(q.contiguous()), q.shape[0], ptr(ids), ids.numel(), int(k),
+                                                 int(min_priority), int(req_tagmask), int(now_us), ptr(idx), ptr(sc),
+                                                 ptr(sc64), C.byref(nb), self._stream()))
+        return nb.value
+
+    def search_resolved(self, q, k: int, min_priority: int = 0, req_tagmask: int = 0, now_us: int = 0):
+        """Device search with the repair step included: CUDA fp32 [nq, dim] in, (idx, score, score64)
+        CUDA tensors out, every row provably exact.  One host sync (reads the inexact counter)."""
+        idx, sc, sc64, inexact, flags = self.search(q, k, min_priority, req_tagmask, now_us, want_score64=True)
+        self.last_fallbacks = int(inexact.item())
+        if self.last_fallbacks:
+            self.refine(q, k, flags.nonzero(), (idx, sc, sc64), min_priority, req_tagmask, now_us)
+        return idx, sc, sc64
+
     def search_exact_noalloc(self, q, k: int, out, query_ids=None, min_priority: int = 0,
                              req_tagmask: int = 0, now_us: int = 0):
         """Exact fp64 search that allocates nothing: for callers that cannot touch the CUDA
