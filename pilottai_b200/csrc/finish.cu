@@ -141,14 +141,16 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_l
     __shared__ uint64_t s_bound[FIN_WARPS];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t q = blockIdx.x;
-    // 1. top-KP of this warp's lists by approximate key.  `bound` = best key any list may have
-    //    dropped: a FULL list (all list_len entries used) may have dropped rows no better than
-    //    its own worst entry; the merged pool, if full, dropped rows no better than its worst.
+    // 1. top-32 of this warp's lists by approximate key.  `bound` = best key that is NOT in the
+    //    pool: a FULL list (all list_len entries used) may have dropped rows no better than its
+    //    own worst entry; every merge drops the elementwise minima of its two inputs, and the
+    //    largest of those is tracked in `drop` (tighter than "the pool's worst entry", and what
+    //    lets k = 32 = pool size be proven).
     const int per_load = 32 / list_len;                    // lists fetched per 32-lane load (1 or 2)
     const int slots = lists_base + ((q / rows_per_group) < groups_rem ? lists_extra : 0);   // lists this query has
     const uint64_t* p = partials + q * (int64_t)slots_alloc * list_len;
     const int nloads = (slots + per_load - 1) / per_load;
-    uint64_t best = 0ull, bound = 0ull;
+    uint64_t best = 0ull, bound = 0ull, drop = 0ull;
     for (int i0 = warp; i0 < nloads; i0 += FIN_WARPS * FIN_MAXLOADS) {
         uint64_t x[FIN_MAXLOADS];
 #pragma unroll
@@ -167,9 +169,12 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_l
             }
             if (mn != 0ull && mn > bound) bound = mn;      // list is full: it may have dropped rows <= mn
             const uint64_t xs = warp_sort64<false>(x[u], lane);
+            const uint64_t lo = best < xs ? best : xs;     // the 32 keys this merge drops
+            drop = drop > lo ? drop : lo;
             best = warp_bitonic_merge_desc(best > xs ? best : xs, lane);
         }
     }
+    bound = bound > drop ? bound : drop;
 #pragma unroll
     for (int j = 16; j > 0; j >>= 1) {
         const uint64_t o = shfl_xor64(bound, j);
@@ -180,12 +185,25 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_l
     __syncthreads();
     // 2. merge the four pools (each sorted descending; read reversed = ascending)
     if (warp == 0) {
+        drop = 0ull;
 #pragma unroll
         for (int w = 1; w < FIN_WARPS; ++w) {
             const uint64_t xs = s_pool[w][31 - lane];
+            const uint64_t lo = best < xs ? best : xs;
+            drop = drop > lo ? drop : lo;
             best = warp_bitonic_merge_desc(best > xs ? best : xs, lane);
             if (s_bound[w] > bound) bound = s_bound[w];
         }
+        if (pool_n < 32) {                                 // entries beyond pool_n are dropped too
+            const uint64_t cut = shfl64(best, pool_n);
+            drop = drop > cut ? drop : cut;
+        }
+#pragma unroll
+        for (int j = 16; j > 0; j >>= 1) {
+            const uint64_t o = shfl_xor64(drop, j);
+            drop = drop > o ? drop : o;
+        }
+        bound = bound > drop ? bound : drop;
     }
     // pool_n = how many survivors get re-scored.
     if (lane >= pool_n) best = 0ull;
@@ -237,14 +255,12 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_l
         __syncthreads();
     }
     if (warp != 0) return;
-    const uint64_t worst = shfl64(best, pool_n - 1);
-    if (worst != 0ull && worst > bound) bound = worst;     // the pool itself is full
     if (gthr) {                                            // rows dropped by a threshold scored below it
         const uint32_t g = __ldcg(gthr + q);
         const uint64_t gk = ((uint64_t)g << 32) | 0xFFFFFFFFull;
         if (g != 0u && gk > bound) bound = gk;
     }
-    const bool pool_full = bound != 0ull;                  // something may have been dropped
+    const bool pool_full = bound != 0ull;                  // something was (or may have been) dropped
     // 3. exact re-score
     const bool valid = best != 0ull;
     double sc = -INFINITY;
