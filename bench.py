@@ -215,7 +215,10 @@ def run_ours(args):
     total_ms = float(ms.item())
     scan_ms, n_scans = loc.profile_read()
     loc.set_profile(False)
-    launches = loc.launch_count() - launches0 + (args.steps if world > 1 else 0)     # + merge kernel
+    # + the merge kernel of the exchange (the peer-memory publish is part of finish_kernel)
+    launches = loc.launch_count() - launches0 + (args.steps if world > 1 else 0)
+    if world > 1:
+        store.check_exchange()
     n_inexact = int(inexact.sum().item()) + sum(int(b["inexact"].item()) for b in store._bufs.values())
     if n_inexact:
         raise SystemExit(f"{n_inexact} queries failed the exactness gap check on synthetic data: result invalid")
@@ -287,7 +290,7 @@ def run_ours(args):
             "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": WORKLOAD, "rows": N_ROWS, "dim": DIM, "queries_per_step": NQ, "k": TOPK,
-                       "sharding": f"rows round-robin over {world} GPU(s)" if world > 1 else "single GPU",
+                       "sharding": f"rows round-robin over {world} GPU(s), exchange {store.exchange}" if world > 1 else "single GPU",
                        "l2": f"corpus ({N_ROWS * DIM * 2 / 1e9:.2f} GB bf16) is larger than L2; 8 distinct query batches cycled"},
             "e2e": {"value": e2e_value, "unit": "queries/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,

@@ -178,6 +178,44 @@ int pilott_mem_compact(pilott_mem_t* h, int64_t now_us, int64_t* kept, uint8_t* 
 int pilott_mem_export(pilott_mem_t* h, uint16_t* vec_bits_host, float* inv_norm_host,
                       int32_t* prio_host, uint64_t* tagmask_host, int64_t* expires_us_host);
 
+/* ---- multi-GPU exchange over NVLink peer memory ---------------------------------------
+ * The exchange step of the row-sharded store without a collective library: every rank maps
+ * every peer's receive buffer (CUDA IPC, one process per GPU on one node), a publish kernel
+ * stores the rank's [2][nq][k] (index, fp64 score) block straight into each peer's buffer and
+ * releases a per-(slot, rank) flag there, and the merge kernel acquires the flags of its slot
+ * before it ranks the world*k candidates of each query.  No reference counterpart (the
+ * reference is single-process).
+ *   create : allocates [4 slots][world][block_bytes] + flags on `device`; handle_out receives
+ *            PILOTT_IPC_HANDLE_BYTES bytes to hand to the other ranks (any transport).
+ *   connect: handles = world * PILOTT_IPC_HANDLE_BYTES bytes in rank order (own entry ignored).
+ *   publish: block_dev = this rank's block (bytes <= block_bytes, multiple of 16), step >= 0.
+ *   merge  : waits for every rank's block of `step`, writes the global top-k like
+ *            pilott_topk_merge_packed.  Per rank, publish(s+1) may be enqueued before merge(s)
+ *            (one batch of overlap), but publish(s+2) must follow merge(s): that rule is what
+ *            makes the four slots enough.  Every rank must take part in every step.
+ *   check  : synchronises the device and reports whether any merge gave up waiting (2 s) for
+ *            a peer -- such a merge wrote "no result" rows instead of hanging. */
+#define PILOTT_IPC_HANDLE_BYTES 64
+typedef struct pilott_xchg pilott_xchg_t;
+int pilott_xchg_create(int device, int rank, int world, int64_t block_bytes, pilott_xchg_t** out,
+                       void* handle_out);
+int pilott_xchg_connect(pilott_xchg_t* x, const void* handles);
+int pilott_xchg_publish(pilott_xchg_t* x, const void* block_dev, int64_t bytes, int64_t step, void* stream);
+int pilott_xchg_merge(pilott_xchg_t* x, int64_t step, int64_t nq, int k, int64_t* out_idx_dev,
+                      float* out_score_dev, double* out_score64_dev, void* stream);
+/* pilott_mem_search + publish in one: finish_kernel stores each query's result row straight into
+ * every rank's exchange buffer as it produces it, and the CTA that finishes last releases the
+ * step's flags -- no separate publish launch, no staging copy.  Same arguments and outputs as
+ * pilott_mem_search (1 <= k <= PILOTT_MAX_FUSED_K, nq >= 1); follow with pilott_xchg_merge(step).
+ * Rows of flagged queries are published as they are: a caller that repairs them
+ * (pilott_mem_search_refine) uses pilott_mem_search + pilott_xchg_publish instead. */
+int pilott_mem_search_publish(pilott_mem_t* h, pilott_xchg_t* x, int64_t step, const float* q_dev, int64_t nq,
+                              int k, int32_t min_prio, uint64_t req_tagmask, int64_t now_us,
+                              int64_t* out_idx_dev, float* out_score_dev, double* out_score64_dev,
+                              int32_t* out_inexact_dev, uint8_t* out_flags_dev, void* stream);
+int pilott_xchg_check(pilott_xchg_t* x);
+int pilott_xchg_destroy(pilott_xchg_t* x);
+
 /* ---- multi-GPU merge ---------------------------------------------------------------
  * After an all-gather of per-shard results: idx/score64 are [n_shards, nq, k]; picks the
  * global top-k per query by (score desc, idx asc).  No reference counterpart: the reference

@@ -12,7 +12,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libpilott_b200.so")
-SOURCES = ["abi.cu", "store_kernels.cu", "scan_generic.cu", "scan_tc.cu", "finish.cu", "route.cu"]
+SOURCES = ["abi.cu", "store_kernels.cu", "scan_generic.cu", "scan_tc.cu", "finish.cu", "route.cu", "xchg.cu"]
 HEADERS = ["common.cuh", "internal.h", os.path.join("..", "..", "include", "pilott_b200.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

@@ -143,6 +143,18 @@ struct pilott_mem {
     int64_t launches = 0;
 };
 
+// Exchange buffers of one rank of a row-sharded store (xchg.cu).
+struct pilott_xchg {
+    int device = 0, rank = 0, world = 1;
+    int64_t block_bytes = 0, flags_off = 0, total_bytes = 0;
+    unsigned char* mine = nullptr;
+    std::vector<unsigned char*> peers;       // peer bases as mapped here (peers[rank] == mine)
+    unsigned char** peers_dev = nullptr;
+    int32_t* err_dev = nullptr;
+    uint32_t* done_dev = nullptr;            // CTA arrival counter of the fused finish + publish
+    bool connected = false;
+};
+
 namespace {
 
 int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
@@ -204,7 +216,8 @@ int pick_kernel(const pilott_mem* h) {
 
 int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t min_prio, uint64_t req,
                 int64_t now_us, int64_t* out_idx, float* out_score, double* out_score64,
-                int32_t* out_inexact, uint8_t* out_flags, cudaStream_t st) {
+                int32_t* out_inexact, uint8_t* out_flags, cudaStream_t st, const pilott_xchg* x = nullptr,
+                int64_t step = 0) {
     if (nq <= 0) return PILOTT_OK;
     if (k < 1 || k > PILOTT_MAX_FUSED_K) return fail(PILOTT_EINVAL, "k must be in [1, 32] for the fused path");
     const int64_t nq_pad = round_up(nq, 256);
@@ -288,6 +301,10 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
     f.err = h->ld * 2.4e-7 > 1e-4 ? h->ld * 2.4e-7 : 1e-4;
     f.out_idx = out_idx; f.out_score = out_score; f.out_score64 = out_score64;
     f.flags = out_flags; f.inexact = out_inexact;
+    if (x) {
+        f.peers = x->peers_dev; f.world = x->world; f.rank = x->rank; f.block_bytes = x->block_bytes;
+        f.flags_off = x->flags_off; f.step = step; f.done_counter = x->done_dev;
+    }
     CK(pilott::launch_finish(f, st));
     h->launches += 2;
     return PILOTT_OK;
@@ -785,6 +802,121 @@ int pilott_topk_merge_packed(const int64_t* packed_dev, int n_shards, int64_t nq
     if (nq > 0 && (!packed_dev || !out_idx_dev || !out_score_dev)) return fail(PILOTT_EINVAL, "NULL pointer");
     CK(pilott::launch_topk_merge(packed_dev, reinterpret_cast<const double*>(packed_dev + nq * k), n_shards, nq, k,
                                  2 * nq * k, out_idx_dev, out_score_dev, out_score64_dev, (cudaStream_t)stream));
+    return PILOTT_OK;
+}
+
+/* ---- exchange over NVLink peer memory (row-sharded store) ---- */
+int pilott_xchg_create(int device, int rank, int world, int64_t block_bytes, pilott_xchg_t** out, void* handle_out) {
+    if (!out || !handle_out) return fail(PILOTT_EINVAL, "NULL output pointer");
+    *out = nullptr;
+    if (world < 1 || world > 64 || rank < 0 || rank >= world) return fail(PILOTT_EINVAL, "bad rank/world");
+    if (block_bytes < 16 || block_bytes % 16) return fail(PILOTT_EINVAL, "block_bytes must be a positive multiple of 16");
+    static_assert(sizeof(cudaIpcMemHandle_t) == PILOTT_IPC_HANDLE_BYTES, "IPC handle size");
+    DeviceGuard g(device);
+    auto* x = new pilott_xchg();
+    x->device = device; x->rank = rank; x->world = world; x->block_bytes = block_bytes;
+    x->flags_off = 4 * (int64_t)world * block_bytes;                 // 4 slots (see xchg.cu)
+    x->total_bytes = x->flags_off + 4 * (int64_t)world * 8;
+    cudaError_t e = cudaMalloc(&x->mine, (size_t)x->total_bytes);
+    if (e == cudaSuccess) e = cudaMemset(x->mine, 0, (size_t)x->total_bytes);
+    if (e == cudaSuccess) e = cudaMalloc(&x->peers_dev, (size_t)world * sizeof(void*));
+    if (e == cudaSuccess) e = cudaMalloc(&x->err_dev, 4);
+    if (e == cudaSuccess) e = cudaMemset(x->err_dev, 0, 4);
+    if (e == cudaSuccess) e = cudaMalloc(&x->done_dev, 4);
+    if (e == cudaSuccess) e = cudaMemset(x->done_dev, 0, 4);
+    cudaIpcMemHandle_t hnd;
+    if (e == cudaSuccess) e = cudaIpcGetMemHandle(&hnd, x->mine);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) {
+        cudaFree(x->mine); cudaFree(x->peers_dev); cudaFree(x->err_dev); cudaFree(x->done_dev);
+        delete x;
+        return fail_cuda(e, "pilott_xchg_create");
+    }
+    memcpy(handle_out, &hnd, sizeof(hnd));
+    *out = x;
+    return PILOTT_OK;
+}
+
+int pilott_xchg_connect(pilott_xchg_t* x, const void* handles) {
+    if (!x || !handles) return fail(PILOTT_EINVAL, "NULL pointer");
+    if (x->connected) return fail(PILOTT_EINVAL, "already connected");
+    DeviceGuard g(x->device);
+    x->peers.assign((size_t)x->world, nullptr);
+    for (int r = 0; r < x->world; ++r) {
+        if (r == x->rank) { x->peers[r] = x->mine; continue; }
+        cudaIpcMemHandle_t hnd;
+        memcpy(&hnd, (const char*)handles + (size_t)r * sizeof(hnd), sizeof(hnd));
+        void* p = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&p, hnd, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            for (int j = 0; j < r; ++j) if (j != x->rank && x->peers[j]) cudaIpcCloseMemHandle(x->peers[j]);
+            x->peers.clear();
+            return fail_cuda(e, "cudaIpcOpenMemHandle (peer buffer)");
+        }
+        x->peers[r] = (unsigned char*)p;
+    }
+    CK(cudaMemcpy(x->peers_dev, x->peers.data(), (size_t)x->world * sizeof(void*), cudaMemcpyHostToDevice));
+    x->connected = true;
+    return PILOTT_OK;
+}
+
+int pilott_mem_search_publish(pilott_mem_t* h, pilott_xchg_t* x, int64_t step, const float* q_dev, int64_t nq, int k,
+                              int32_t min_prio, uint64_t req_tagmask, int64_t now_us, int64_t* out_idx_dev,
+                              float* out_score_dev, double* out_score64_dev, int32_t* out_inexact_dev,
+                              uint8_t* out_flags_dev, void* stream) {
+    if (!h || !x) return fail(PILOTT_EINVAL, "handle is NULL");
+    if (!x->connected) return fail(PILOTT_EINVAL, "exchange is not connected");
+    if (x->device != h->device) return fail(PILOTT_EINVAL, "store and exchange live on different devices");
+    if (nq < 1 || step < 0) return fail(PILOTT_EINVAL, "nq must be >= 1 and step >= 0 (every rank publishes every step)");
+    if (2 * nq * k * 8 > x->block_bytes) return fail(PILOTT_EINVAL, "[2, nq, k] block exceeds block_bytes");
+    if (!q_dev || !out_idx_dev || !out_score_dev) return fail(PILOTT_EINVAL, "NULL query or output pointer");
+    DeviceGuard g(h->device);
+    return search_core(h, q_dev, nq, k, min_prio, req_tagmask, now_us, out_idx_dev, out_score_dev,
+                       out_score64_dev, out_inexact_dev, out_flags_dev, (cudaStream_t)stream, x, step);
+}
+
+int pilott_xchg_publish(pilott_xchg_t* x, const void* block_dev, int64_t bytes, int64_t step, void* stream) {
+    if (!x || !block_dev) return fail(PILOTT_EINVAL, "NULL pointer");
+    if (!x->connected) return fail(PILOTT_EINVAL, "exchange is not connected");
+    if (bytes < 16 || bytes % 16 || bytes > x->block_bytes) return fail(PILOTT_EINVAL, "bytes must be a multiple of 16 within block_bytes");
+    if (step < 0) return fail(PILOTT_EINVAL, "step is negative");
+    DeviceGuard g(x->device);
+    CK(pilott::launch_xchg_publish(x->peers_dev, x->world, x->rank, x->block_bytes, x->flags_off, block_dev, bytes,
+                                   step, (cudaStream_t)stream));
+    return PILOTT_OK;
+}
+
+int pilott_xchg_merge(pilott_xchg_t* x, int64_t step, int64_t nq, int k, int64_t* out_idx_dev, float* out_score_dev,
+                      double* out_score64_dev, void* stream) {
+    if (!x) return fail(PILOTT_EINVAL, "NULL pointer");
+    if (!x->connected) return fail(PILOTT_EINVAL, "exchange is not connected");
+    if (nq < 0 || k < 1 || step < 0) return fail(PILOTT_EINVAL, "bad merge shape");
+    if ((int64_t)x->world * k > 2048) return fail(PILOTT_EINVAL, "world * k must be <= 2048");
+    if (2 * nq * k * 8 > x->block_bytes) return fail(PILOTT_EINVAL, "[2, nq, k] block exceeds block_bytes");
+    if (nq > 0 && (!out_idx_dev || !out_score_dev)) return fail(PILOTT_EINVAL, "NULL output pointer");
+    DeviceGuard g(x->device);
+    CK(pilott::launch_xchg_merge(x->mine, x->world, x->block_bytes, x->flags_off, step, nq, k, out_idx_dev,
+                                 out_score_dev, out_score64_dev, x->err_dev, (cudaStream_t)stream));
+    return PILOTT_OK;
+}
+
+int pilott_xchg_check(pilott_xchg_t* x) {
+    if (!x) return fail(PILOTT_EINVAL, "NULL pointer");
+    DeviceGuard g(x->device);
+    int32_t err = 0;
+    CK(cudaMemcpy(&err, x->err_dev, 4, cudaMemcpyDeviceToHost));      // synchronises with prior work
+    if (err) return fail(PILOTT_ECUDA, "a merge waited 2 s for a peer's block and gave up (peer stalled or died)");
+    return PILOTT_OK;
+}
+
+int pilott_xchg_destroy(pilott_xchg_t* x) {
+    if (!x) return PILOTT_OK;
+    DeviceGuard g(x->device);
+    cudaDeviceSynchronize();
+    for (int r = 0; r < (int)x->peers.size(); ++r)
+        if (r != x->rank && x->peers[r]) cudaIpcCloseMemHandle(x->peers[r]);
+    cudaFree(x->mine); cudaFree(x->peers_dev); cudaFree(x->err_dev); cudaFree(x->done_dev);
+    delete x;
     return PILOTT_OK;
 }
 

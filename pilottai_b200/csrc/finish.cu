@@ -134,7 +134,8 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_l
               int64_t* __restrict__ out_idx,
               float* __restrict__ out_score, double* __restrict__ out_score64,
               uint8_t* __restrict__ flags, int32_t* __restrict__ inexact, int stage_rows,
-              const uint32_t* __restrict__ gthr) {
+              const uint32_t* __restrict__ gthr, unsigned char* const* __restrict__ peers, int world, int rank,
+              int64_t block_bytes, int64_t flags_off, int64_t step, uint32_t* __restrict__ done_counter) {
     extern __shared__ __align__(16) unsigned char s_rows[];     // [pool_n + 1][ld*2 + 16] when stage_rows
     __shared__ uint64_t s_pool[FIN_WARPS][32];
     __shared__ double s_part[3][FIN_WARPS][32];              // per-warp pair sums of (dot, nq, nm) per candidate
@@ -290,6 +291,36 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_l
         out_score[q * k + lane] = ok ? (float)sc : -INFINITY;
         if (out_score64) out_score64[q * k + lane] = ok ? sc : -INFINITY;
     }
+    // 4b. row-sharded store: the result row goes straight into every rank's exchange buffer over
+    // NVLink ([slot][rank] block = [2][nq][k] words: indices, fp64 score bits); the CTA that
+    // finishes last releases the step's flag on every rank (fence / counter / fence: the pattern
+    // of a last-block reduction, at system scope).
+    if (peers) {
+        const int slot = (int)(step & 3);
+        if (lane < k) {
+            const bool ok = seq != INT64_MAX;
+            const int64_t iw = ok ? seq * seq_mul + seq_add : -1;
+            const int64_t sw = __double_as_longlong(ok ? sc : -INFINITY);
+            for (int p = 0; p < world; ++p) {
+                int64_t* blk = reinterpret_cast<int64_t*>(peers[p] + ((int64_t)slot * world + rank) * block_bytes);
+                blk[q * k + lane] = iw;
+                blk[nq * k + q * k + lane] = sw;
+            }
+            __threadfence_system();
+        }
+        __syncwarp();
+        if (lane == 0) {
+            const uint32_t old = atomicAdd(done_counter, 1u);
+            if (old == (uint32_t)(nq - 1)) {
+                *done_counter = 0u;                                // ready for the next launch
+                __threadfence_system();
+                for (int p = 0; p < world; ++p) {
+                    uint64_t* flag = reinterpret_cast<uint64_t*>(peers[p] + flags_off) + (int64_t)slot * world + rank;
+                    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(flag), "l"((uint64_t)(step + 1)) : "memory");
+                }
+            }
+        }
+    }
     // 5. gap check: every row dropped by the approximate pass has approximate score <=
     // the worst kept one; it cannot reach the exact k-th score if the gap exceeds err.
     const double e_k = __longlong_as_double((long long)shfl64((uint64_t)__double_as_longlong(sc), k - 1));
@@ -317,7 +348,8 @@ cudaError_t launch_finish(const FinishArgs& a, cudaStream_t st) {
         a.partials, a.slots, a.list_len, a.pool_n, a.rows_per_group, a.lists_base, a.groups_rem, a.lists_extra,
         (const __nv_bfloat16*)a.qb, (const __nv_bfloat16*)a.vec, a.ld, a.nq,
         a.capacity, a.head, a.base_seq, a.seq_mul, a.seq_add, a.k, a.err, a.out_idx, a.out_score, a.out_score64,
-        a.flags, a.inexact, stage_rows, a.gthr);
+        a.flags, a.inexact, stage_rows, a.gthr, a.peers, a.world, a.rank, a.block_bytes, a.flags_off, a.step,
+        a.done_counter);
     return cudaGetLastError();
 }
 

@@ -67,9 +67,22 @@ struct FinishArgs {
     int64_t seq_mul, seq_add;   // reported index = seq * seq_mul + seq_add
     int64_t* out_idx; float* out_score; double* out_score64;
     uint8_t* flags; int32_t* inexact;
+    // Row-sharded store: when `peers` is set the kernel also stores every result row into each
+    // rank's exchange buffer over NVLink (xchg.cu layout) and the last CTA releases the flags.
+    unsigned char* const* peers = nullptr;
+    int world = 1, rank = 0;
+    int64_t block_bytes = 0, flags_off = 0, step = 0;
+    uint32_t* done_counter = nullptr;
 };
 cudaError_t launch_finish(const FinishArgs& a, cudaStream_t st);
 
+
+// exchange over NVLink peer memory (xchg.cu)
+cudaError_t launch_xchg_publish(unsigned char* const* peers_dev, int world, int rank, int64_t block_bytes,
+                                int64_t flags_off, const void* src, int64_t bytes, int64_t step, cudaStream_t st);
+cudaError_t launch_xchg_merge(const void* mine, int world, int64_t block_bytes, int64_t flags_off, int64_t step,
+                              int64_t nq, int k, int64_t* out_idx, float* out_score, double* out_score64,
+                              int32_t* err_word, cudaStream_t st);
 
 // second-chance pass for flagged queries (finish.cu); the COLLECT scan runs between the two
 cudaError_t launch_refine_prepare(const void* qb, const int32_t* qids, int64_t nsel, int64_t nsel_pad, int ld,

@@ -3,20 +3,35 @@
 SURVEY.md section 8e: global insertion index i lives on rank i % world at local sequence
 i // world (round-robin keeps streaming inserts and ring eviction balanced).  A search is
   local fused search (exact top-k of the shard, fp64 scores, GLOBAL indices)
-  -> all_gather of the [Q, k] (index, score) lists  (NCCL on GPUs, gloo in CPU tests)
-  -> pilott_topk_merge: global top-k by (score desc, index asc)
+  -> exchange of the [Q, k] (index, score) blocks
+  -> global top-k by (score desc, index asc)
 which is identical to what one store holding every row returns.  There is no reference
 counterpart: the reference is single-process.
+
+Two exchanges:
+  "p2p"  (default on GPUs of one node) -- pilott_xchg_*: every rank maps every peer's receive
+         buffer (CUDA IPC); a publish kernel stores the block straight into the peers over
+         NVLink and releases a flag, the merge kernel acquires the flags and ranks.  No
+         collective library on the data path, no extra SMs taken from the scan kernel.
+  "nccl" -- one all_gather_into_tensor of the packed block + pilott_topk_merge_packed; with two
+         slots the exchange of batch i overlaps the local search of batch i+1.  Also the
+         fallback when peer mapping is not available (PILOTT_EXCHANGE=nccl forces it).
 """
 from __future__ import annotations
 
+import ctypes as C
+import os
 from typing import Optional
 
 import numpy as np
 import torch
 import torch.distributed as dist
 
+from . import _lib
+from ._lib import check, ptr
 from .store import SemanticStore, topk_merge_packed
+
+IPC_HANDLE_BYTES = 64
 
 
 def shard_rows(first_global: int, n: int, rank: int, world: int) -> np.ndarray:
@@ -27,8 +42,14 @@ def shard_rows(first_global: int, n: int, rank: int, world: int) -> np.ndarray:
 
 class ShardedSemanticStore:
     def __init__(self, dim: int, capacity: int, rank: int, world: int, device: int,
-                 group: Optional[dist.ProcessGroup] = None):
+                 group: Optional[dist.ProcessGroup] = None, exchange: str = "auto"):
         self.rank, self.world, self.group = rank, world, group
+        if exchange == "auto":
+            exchange = os.environ.get("PILOTT_EXCHANGE", "p2p")
+        if exchange not in ("p2p", "nccl"):
+            raise ValueError("exchange must be 'auto', 'p2p' or 'nccl'")
+        self.exchange = exchange if world > 1 else "none"
+        self._xchg = {}                                 # (nq, k) -> [handle, next step]
         self.local = SemanticStore(dim, (capacity + world - 1) // world, device)
         self.local.set_sequence_map(world, rank)
         self.dim, self.device = dim, device
@@ -61,21 +82,62 @@ class ShardedSemanticStore:
                 "flags": torch.empty(nq, dtype=torch.uint8, device=dev),
                 "inexact": torch.zeros(1, dtype=torch.int32, device=dev),
                 "gathered": torch.empty((self.world, 2, nq, k), dtype=torch.int64, device=dev),
+                "m_idx": torch.empty((nq, k), dtype=torch.int64, device=dev),
+                "m_sc": torch.empty((nq, k), dtype=torch.float32, device=dev),
+                "m_sc64": torch.empty((nq, k), dtype=torch.float64, device=dev),
             }
         return self._bufs[key]
 
+    def _exchange_for(self, nq: int, k: int):
+        """Peer-mapped exchange buffers for [2, nq, k] blocks (created collectively, once per shape).
+        Falls back to the NCCL exchange for good if any rank cannot map its peers."""
+        key = (nq, k)
+        if key in self._xchg:
+            return self._xchg[key]
+        lib = _lib.load()
+        handle = C.create_string_buffer(IPC_HANDLE_BYTES)
+        x = C.c_void_p()
+        rc = lib.pilott_xchg_create(self.device, self.rank, self.world, 2 * nq * k * 8, C.byref(x), handle)
+        gathered = [None] * self.world
+        dist.all_gather_object(gathered, handle.raw if rc == 0 else None, group=self.group)
+        ok = rc == 0 and all(h is not None for h in gathered)
+        if ok:
+            ok = lib.pilott_xchg_connect(x, b"".join(gathered)) == 0
+        flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device=torch.device("cuda", self.device))
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+        if int(flag.item()) == 0:
+            if rc == 0:
+                lib.pilott_xchg_destroy(x)
+            self.exchange = "nccl"
+            return None
+        self._xchg[key] = [x, 0]
+        return self._xchg[key]
+
     def search_begin(self, q: torch.Tensor, k: int, slot: int = 0, resolve: bool = False, **flt):
-        """Local search + ONE asynchronous all-gather of the packed (index, score) block.
-        Returns a ticket for search_end(); with two slots a caller overlaps the exchange of
-        batch i with the local search of batch i+1.  resolve=True reads the local inexact
-        counter (one host sync) and repairs flagged queries before the exchange; with
-        resolve=False the caller checks the counter search_end() returns."""
+        """Local search, then the block is sent on its way (publish kernel over NVLink, or ONE
+        asynchronous all-gather).  Returns a ticket for search_end(), which merges.  With two
+        buffer slots a caller overlaps the exchange of batch i with the local search of batch i+1
+        (at most ONE search_begin ahead of the matching search_end: the exchange has 4 slots).
+        resolve=True reads the local inexact counter (one host sync) and repairs flagged queries
+        before the exchange; with resolve=False the caller checks the counter search_end() returns."""
         b = self._buffers(q.shape[0], k, q.device, slot)
+        xs = self._exchange_for(q.shape[0], k) if self.exchange == "p2p" else None
+        if xs is not None and not resolve:
+            # fused: finish_kernel stores the result rows into every rank's buffer as it produces them
+            step = xs[1]
+            xs[1] += 1
+            self.local.search_publish_into(xs[0], step, q, k, b["idx"], b["sc"], b["sc64"], b["inexact"], b["flags"], **flt)
+            return b, ("p2p", xs[0], step, q.shape[0], k)
         self.local.search_into(q, k, b["idx"], b["sc"], b["sc64"], b["inexact"], b["flags"], **flt)
         if resolve and int(b["inexact"].item()):
             self.local.refine(q, k, b["flags"].nonzero(), (b["idx"], b["sc"], b["sc64"]), **flt)
             b["inexact"].zero_()
         work = None
+        if xs is not None:                               # repaired rows: publish the block with its own kernel
+            step = xs[1]
+            xs[1] += 1
+            check(_lib.load().pilott_xchg_publish(xs[0], ptr(b["mine"]), b["mine"].numel() * 8, step, self.local._stream()))
+            return b, ("p2p", xs[0], step, q.shape[0], k)
         if self.world > 1:
             work = dist.all_gather_into_tensor(b["gathered"], b["mine"], group=self.group, async_op=True)
         return b, work
@@ -84,9 +146,20 @@ class ShardedSemanticStore:
         b, work = ticket
         if self.world == 1:
             return b["idx"], b["sc"], b["sc64"], b["inexact"]
-        work.wait()
-        m_idx, m_sc, m_sc64 = topk_merge_packed(b["gathered"])
-        return m_idx, m_sc, m_sc64, b["inexact"]
+        if isinstance(work, tuple):                      # peer-memory exchange: the block is already on its way
+            _, x, step, nq, k = work
+            check(_lib.load().pilott_xchg_merge(x, step, nq, k, ptr(b["m_idx"]), ptr(b["m_sc"]), ptr(b["m_sc64"]),
+                                                self.local._stream()))
+        else:
+            work.wait()
+            topk_merge_packed(b["gathered"], out=(b["m_idx"], b["m_sc"], b["m_sc64"]))
+        return b["m_idx"], b["m_sc"], b["m_sc64"], b["inexact"]
+
+    def check_exchange(self) -> None:
+        """Synchronises and raises if a p2p merge ever gave up waiting for a peer."""
+        lib = _lib.load()
+        for x, _ in self._xchg.values():
+            check(lib.pilott_xchg_check(x))
 
     def search(self, q: torch.Tensor, k: int, **flt):
         """q: CUDA fp32 [Q, dim], same on every rank.  Returns (idx, score, score64) on every rank,
@@ -94,4 +167,8 @@ class ShardedSemanticStore:
         return self.search_end(self.search_begin(q, k, 0, True, **flt))
 
     def close(self):
+        lib = _lib.load()
+        for x, _ in self._xchg.values():
+            lib.pilott_xchg_destroy(x)
+        self._xchg = {}
         self.local.close()

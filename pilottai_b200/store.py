@@ -179,6 +179,14 @@ class SemanticStore:
                                           int(req_tagmask), int(now_us), ptr(idx), ptr(sc), ptr(sc64),
                                           ptr(inexact), ptr(flags), self._stream()))
 
+    def search_publish_into(self, xchg, step: int, q, k, idx, sc, sc64, inexact, flags, min_priority=0,
+                            req_tagmask=0, now_us=0):
+        """search_into for a row-sharded store: finish_kernel also stores the result rows into every
+        rank's exchange buffer and releases the step's flags (pilott_mem_search_publish)."""
+        check(self._lib.pilott_mem_search_publish(self._h, xchg, int(step), ptr(q), q.shape[0], int(k),
+                                                  int(min_priority), int(req_tagmask), int(now_us), ptr(idx), ptr(sc),
+                                                  ptr(sc64), ptr(inexact), ptr(flags), self._stream()))
+
     def search_exact(self, q, k: int, query_ids=None, out=None, min_priority: int = 0, req_tagmask: int = 0,
                      now_us: int = 0):
         """Brute-force fp64 search on the device (any k).  q: CUDA fp32 [nq, dim]."""

@@ -1,5 +1,6 @@
 """GPU tests of the sharded path: the merge kernel (K6) on one GPU, and -- when the box has
-two or more GPUs -- the full NCCL path (one process per GPU) against the CPU oracle."""
+two or more GPUs -- the full path (one process per GPU) with both exchanges, the NVLink peer-memory
+one and the NCCL one, against the CPU oracle."""
 import os
 import socket
 
@@ -44,7 +45,7 @@ def test_topk_merge_kernel_matches_host_rule(torch_cuda):
         assert np.array_equal(gi[q], want_i) and np.array_equal(gs64[q], want_s)
 
 
-def _worker(rank, world, port, n, dim, nq, k, out):
+def _worker(rank, world, port, n, dim, nq, k, out, exchange):
     import torch
     import torch.distributed as dist
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
@@ -54,20 +55,39 @@ def _worker(rank, world, port, n, dim, nq, k, out):
     x = synth.corpus(n, dim, seed=3, dup_frac=0.01)
     prio, tag, exp = synth.metadata(n, seed=5)
     q = torch.from_numpy(synth.queries(nq, dim, seed=4)).cuda()
-    st = ShardedSemanticStore(dim, n, rank, world, rank)
+    st = ShardedSemanticStore(dim, n, rank, world, rank, exchange=exchange)
     for lo in range(0, n, 7000):
         hi = min(n, lo + 7000)
         st.append(x[lo:hi], prio[lo:hi], tag[lo:hi], exp[lo:hi])
-    idx, sc, sc64, inexact = st.search(q, k, min_priority=1, now_us=1_000_000)
+    # several steps in a row: the p2p exchange alternates between its two slots and every merge
+    # has to wait for the blocks of ITS step
+    for rep in range(5):
+        idx, sc, sc64, inexact = st.search(q if rep % 2 == 0 else q.flip(0).contiguous(), k, min_priority=1, now_us=1_000_000)
     torch.cuda.synchronize()
+    st.check_exchange()
+    assert st.exchange == exchange                      # no silent fallback to the other transport
     assert int(inexact.item()) == 0
+    # pipelined form (what bench.py runs): begin(i+1) before end(i); with the peer-memory exchange the
+    # result rows are stored into the peers by finish_kernel itself
+    want_i, want_s = idx.clone(), sc64.clone()
+    qf = q.flip(0).contiguous()
+    for rep in range(3):
+        t0 = st.search_begin(q, k, slot=0, min_priority=1, now_us=1_000_000)
+        t1 = st.search_begin(qf, k, slot=1, min_priority=1, now_us=1_000_000)
+        i0, _, s0, _ = st.search_end(t0)
+        i1, _, s1, _ = st.search_end(t1)
+        torch.cuda.synchronize()
+        assert torch.equal(i0, want_i) and torch.equal(s0, want_s)
+        assert torch.equal(i1.flip(0), want_i) and torch.equal(s1.flip(0), want_s)
+    st.check_exchange()
     if rank == 0:
         np.save(out + "_i.npy", idx.cpu().numpy()); np.save(out + "_s.npy", sc64.cpu().numpy())
     st.close()
     dist.destroy_process_group()
 
 
-def test_nccl_sharded_search_equals_single_store(torch_cuda, tmp_path):
+@pytest.mark.parametrize("exchange", ["p2p", "nccl"])
+def test_sharded_search_equals_single_store(torch_cuda, tmp_path, exchange):
     torch = torch_cuda
     world = min(torch.cuda.device_count(), 4)
     if world < 2:
@@ -76,7 +96,7 @@ def test_nccl_sharded_search_equals_single_store(torch_cuda, tmp_path):
     n, dim, nq, k = 30_000, 256, 64, 10
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
     out = str(tmp_path / "merged")
-    mp.spawn(_worker, args=(world, port, n, dim, nq, k, out), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, port, n, dim, nq, k, out, exchange), nprocs=world, join=True)
     whole = OracleStore(dim, n)
     prio, tag, exp = synth.metadata(n, seed=5)
     whole.append(synth.corpus(n, dim, seed=3, dup_frac=0.01), prio, tag, exp)
