@@ -306,10 +306,10 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_l
                 blk[q * k + lane] = iw;
                 blk[nq * k + q * k + lane] = sw;
             }
-            __threadfence_system();
         }
-        __syncwarp();
+        __syncwarp();                                              // orders the lanes' stores before lane 0's fence
         if (lane == 0) {
+            __threadfence_system();                                // ONE fence per CTA (cumulative), not one per lane
             const uint32_t old = atomicAdd(done_counter, 1u);
             if (old == (uint32_t)(nq - 1)) {
                 *done_counter = 0u;                                // ready for the next launch

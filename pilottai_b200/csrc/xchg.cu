@@ -44,9 +44,9 @@ xchg_publish_kernel(unsigned char* const* __restrict__ peers, int world, int ran
     uint4* out = reinterpret_cast<uint4*>(base + ((int64_t)slot * world + rank) * block_bytes);
     const int64_t n16 = bytes / 16;
     for (int64_t i = threadIdx.x; i < n16; i += blockDim.x) out[i] = src[i];
-    __threadfence_system();
-    __syncthreads();
+    __syncthreads();                                   // the CTA's stores happen before thread 0's fence
     if (threadIdx.x == 0) {
+        __threadfence_system();                        // one cumulative fence, then the release
         uint64_t* flag = reinterpret_cast<uint64_t*>(base + flags_off) + (int64_t)slot * world + rank;
         st_release_sys(flag, (uint64_t)(step + 1));
     }
