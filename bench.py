@@ -229,23 +229,70 @@ def run_ours(args):
     qhost.copy_(qpool.cpu())
     qnp = qhost.numpy()
     h2d, d2h = NQ * DIM * 4, NQ * TOPK * (8 + 4)
+    # Both forms keep two batches in flight: the H2D copy of batch i+1 and the D2H copy of batch i-1
+    # overlap the search of batch i.  Every step's inputs come from pinned host memory and every
+    # step's results are read back to the host inside the timed region.
     if world == 1:
-        def e2e_step(i):
-            return loc.search(qnp[i % Q_POOL], TOPK)
         d2h = NQ * TOPK * (8 + 8 + 4) + NQ + 8          # idx, fp64 + fp32 scores, flags, counter
-    else:
-        qdev = torch.empty((NQ, DIM), dtype=torch.float32, device=dev)
 
-        def e2e_step(i):
-            qdev.copy_(qhost[i % Q_POOL], non_blocking=True)
-            m_idx, m_sc, _, _ = store.search(qdev, TOPK)
-            return m_idx.cpu(), m_sc.cpu()
-    for i in range(min(3, args.warmup)):
-        e2e_step(i)
+        def e2e_run(n):
+            for i in range(n):
+                loc.search_host_begin(i % 2, qnp[i % Q_POOL], TOPK)      # pilott_mem_search_host_begin
+                if i > 0:
+                    loc.search_host_end((i - 1) % 2)                    # ... _end: waits, repairs, copies out
+            loc.search_host_end((n - 1) % 2)
+    else:
+        h2d_s, d2h_s = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+        qdev = [torch.empty((NQ, DIM), dtype=torch.float32, device=dev) for _ in range(2)]
+        out_i = [torch.empty((NQ, TOPK), dtype=torch.int64).pin_memory() for _ in range(2)]
+        out_s = [torch.empty((NQ, TOPK), dtype=torch.float32).pin_memory() for _ in range(2)]
+        out_c = [torch.zeros(1, dtype=torch.int32).pin_memory() for _ in range(2)]
+        ev_h2d = [torch.cuda.Event() for _ in range(2)]
+        ev_used = [torch.cuda.Event() for _ in range(2)]
+        ev_done = [torch.cuda.Event() for _ in range(2)]
+        ev_d2h = [torch.cuda.Event() for _ in range(2)]
+        d2h = NQ * TOPK * (8 + 4) + 4
+
+        def e2e_run(n):
+            main = torch.cuda.current_stream(dev)
+            tickets = [None, None]
+            flagged = 0
+
+            def finish(j):
+                s = j % 2
+                m_idx, m_sc, _, cnt = store.search_end(tickets[s])
+                ev_done[s].record(main)
+                d2h_s.wait_event(ev_done[s])
+                with torch.cuda.stream(d2h_s):
+                    out_i[s].copy_(m_idx, non_blocking=True)
+                    out_s[s].copy_(m_sc, non_blocking=True)
+                    out_c[s].copy_(cnt, non_blocking=True)
+                ev_d2h[s].record(d2h_s)
+
+            for i in range(n):
+                s = i % 2
+                if i >= 2:
+                    ev_d2h[s].synchronize()                          # results of batch i-2 are on the host
+                    flagged += int(out_c[s].item())
+                    h2d_s.wait_event(ev_used[s])                     # its queries were consumed
+                with torch.cuda.stream(h2d_s):
+                    qdev[s].copy_(qhost[i % Q_POOL], non_blocking=True)
+                ev_h2d[s].record(h2d_s)
+                main.wait_event(ev_h2d[s])
+                tickets[s] = store.search_begin(qdev[s], TOPK, slot=s)
+                ev_used[s].record(main)
+                if i > 0:
+                    finish(i - 1)
+            finish(n - 1)
+            for s in range(2):
+                ev_d2h[s].synchronize()
+                flagged += int(out_c[s].item())
+            if flagged:
+                raise SystemExit(f"{flagged} queries failed the exactness gap check on synthetic data: result invalid")
+    e2e_run(max(4, min(8, args.warmup)))
     barrier()
     t0 = time.perf_counter()
-    for i in range(args.steps):
-        e2e_step(i)
+    e2e_run(args.steps)
     torch.cuda.synchronize()
     dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
     if world > 1:

@@ -109,6 +109,18 @@ int pilott_mem_search_host(pilott_mem_t* h, const float* q_host, int64_t nq, int
                            int32_t min_prio, uint64_t req_tagmask, int64_t now_us,
                            int64_t* out_idx_host, float* out_score_host, double* out_score64_host,
                            int32_t* n_fallback);
+/* The host-buffer search split in two, so that a caller can keep several batches in flight:
+ * _begin copies the queries to the device on a copy stream, enqueues the search behind it on the
+ * handle's compute stream and the copy of the results back on a second copy stream, and returns
+ * without waiting; _end waits for that slot's results, runs the second-chance pass if the batch
+ * flagged queries, and fills the outputs exactly like pilott_mem_search_host.  With two slots the
+ * H2D copy of batch i+1 and the D2H copy of batch i-1 overlap the search of batch i.  4 slots per
+ * handle; a slot is busy from _begin to _end; q_host must stay valid until _end when it is
+ * page-locked memory (pageable memory is copied into a pinned staging buffer inside _begin). */
+int pilott_mem_search_host_begin(pilott_mem_t* h, int slot, const float* q_host, int64_t nq, int k,
+                                 int32_t min_prio, uint64_t req_tagmask, int64_t now_us);
+int pilott_mem_search_host_end(pilott_mem_t* h, int slot, int64_t* out_idx_host, float* out_score_host,
+                               double* out_score64_host, int32_t* n_fallback);
 /* Brute-force fp64 search (any k >= 1): every candidate row scored in the oracle's order.
  * Slow path for flagged queries / large k.  query_ids_dev (int32[nsel], may be NULL = all
  * nq) selects which rows of q/out to process. */

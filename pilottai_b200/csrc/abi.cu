@@ -112,6 +112,21 @@ struct DeviceGuard {
 // address is looked up per device by noalloc_scratch() below.
 static __device__ __align__(256) unsigned char g_noalloc_scratch[PILOTT_NOALLOC_SCRATCH_BYTES];
 
+// One in-flight host-buffer search (pilott_mem_search_host_begin / _end).
+struct HostSlot {
+    DevBuf q_dev, res_dev;
+    HostBuf q_host, res_host;
+    cudaEvent_t e_h2d = nullptr, e_done = nullptr, e_d2h = nullptr;
+    int64_t nq = 0;
+    int k = 0;
+    int32_t min_prio = 0;
+    uint64_t req = 0;
+    int64_t now_us = 0;
+    bool busy = false, fused = true;
+    size_t off_s64 = 0, off_s = 0, off_f = 0, off_c = 0, rtot = 0;
+};
+constexpr int HOST_SLOTS = 4;
+
 struct pilott_mem {
     int dim = 0, ld = 0, device = 0, num_sms = 0;
     int64_t capacity = 0, cap_pad = 0;
@@ -128,6 +143,8 @@ struct pilott_mem {
     DevBuf qbuf, partials, gthr, exact_scratch, stage_dev, result_dev, misc_dev, refine, result_ids;
     HostBuf stage_host;
     cudaStream_t own_stream = nullptr;
+    cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;   // copy streams of the pipelined host path
+    HostSlot hslot[HOST_SLOTS];
     CUtensorMap map_c;
     bool tc_ok = false;
     int opt_kernel = 0;     // 0 auto, 1 generic, 2 tc 1-CTA, 3 tc pair
@@ -483,6 +500,14 @@ int pilott_mem_destroy(pilott_mem_t* h) {
     h->result_dev.release(); h->misc_dev.release(); h->refine.release(); h->result_ids.release();
     h->stage_host.release();
     for (cudaEvent_t e : h->ev) cudaEventDestroy(e);
+    for (auto& sl : h->hslot) {
+        sl.q_dev.release(); sl.res_dev.release(); sl.q_host.release(); sl.res_host.release();
+        if (sl.e_h2d) cudaEventDestroy(sl.e_h2d);
+        if (sl.e_done) cudaEventDestroy(sl.e_done);
+        if (sl.e_d2h) cudaEventDestroy(sl.e_d2h);
+    }
+    if (h->h2d_stream) cudaStreamDestroy(h->h2d_stream);
+    if (h->d2h_stream) cudaStreamDestroy(h->d2h_stream);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     delete h;
     return PILOTT_OK;
@@ -710,6 +735,103 @@ int pilott_mem_search_host(pilott_mem_t* h, const float* q_host, int64_t nq, int
     memcpy(out_idx_host, rh, ib);
     memcpy(out_score_host, rh + off_s, sb);
     if (out_score64_host) memcpy(out_score64_host, rh + off_s64, s64b);
+    return PILOTT_OK;
+}
+
+int pilott_mem_search_host_begin(pilott_mem_t* h, int slot, const float* q_host, int64_t nq, int k, int32_t min_prio,
+                                 uint64_t req_tagmask, int64_t now_us) {
+    if (!h) return fail(PILOTT_EINVAL, "handle is NULL");
+    if (slot < 0 || slot >= HOST_SLOTS) return fail(PILOTT_EINVAL, "slot must be in [0, 4)");
+    if (nq < 1) return fail(PILOTT_EINVAL, "nq must be >= 1");
+    if (k < 1) return fail(PILOTT_EINVAL, "k must be >= 1");
+    if (!q_host) return fail(PILOTT_EINVAL, "NULL query pointer");
+    HostSlot& sl = h->hslot[slot];
+    if (sl.busy) return fail(PILOTT_EINVAL, "slot is in flight: call pilott_mem_search_host_end first");
+    DeviceGuard g(h->device);
+    if (!h->h2d_stream) CK(cudaStreamCreateWithFlags(&h->h2d_stream, cudaStreamNonBlocking));
+    if (!h->d2h_stream) CK(cudaStreamCreateWithFlags(&h->d2h_stream, cudaStreamNonBlocking));
+    if (!sl.e_h2d) {
+        CK(cudaEventCreateWithFlags(&sl.e_h2d, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&sl.e_done, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&sl.e_d2h, cudaEventDisableTiming));
+    }
+    const size_t qb = (size_t)nq * h->dim * 4;
+    const size_t ib = (size_t)nq * k * 8, sb = (size_t)nq * k * 4, fb = (size_t)round_up(nq, 8);
+    sl.off_s64 = ib; sl.off_s = 2 * ib; sl.off_f = sl.off_s + (size_t)round_up((int64_t)sb, 8); sl.off_c = sl.off_f + fb;
+    sl.rtot = sl.off_c + 8;
+    int rc = sl.q_dev.ensure(qb);
+    if (rc) return rc;
+    rc = sl.res_dev.ensure(sl.rtot);
+    if (rc) return rc;
+    rc = sl.res_host.ensure(sl.rtot);
+    if (rc) return rc;
+    const void* src = q_host;
+    if (!is_pinned(q_host)) {                       // pageable: stage through the slot's pinned buffer
+        rc = sl.q_host.ensure(qb);
+        if (rc) return rc;
+        memcpy(sl.q_host.p, q_host, qb);
+        src = sl.q_host.p;
+    }
+    CK(cudaMemcpyAsync(sl.q_dev.p, src, qb, cudaMemcpyHostToDevice, h->h2d_stream));
+    CK(cudaEventRecord(sl.e_h2d, h->h2d_stream));
+    cudaStream_t st = h->own_stream;
+    CK(cudaStreamWaitEvent(st, sl.e_h2d, 0));
+    char* rd = (char*)sl.res_dev.p;
+    sl.nq = nq; sl.k = k; sl.min_prio = min_prio; sl.req = req_tagmask; sl.now_us = now_us;
+    sl.fused = k <= PILOTT_MAX_FUSED_K;
+    if (sl.fused)
+        rc = search_core(h, (const float*)sl.q_dev.p, nq, k, min_prio, req_tagmask, now_us, (int64_t*)rd,
+                         (float*)(rd + sl.off_s), (double*)(rd + sl.off_s64), (int32_t*)(rd + sl.off_c),
+                         (uint8_t*)(rd + sl.off_f), st);
+    else
+        rc = exact_core(h, (const float*)sl.q_dev.p, nq, nullptr, nq, k, min_prio, req_tagmask, now_us, (int64_t*)rd,
+                        (float*)(rd + sl.off_s), (double*)(rd + sl.off_s64), st);
+    if (rc) return rc;
+    CK(cudaEventRecord(sl.e_done, st));
+    CK(cudaStreamWaitEvent(h->d2h_stream, sl.e_done, 0));
+    CK(cudaMemcpyAsync(sl.res_host.p, rd, sl.rtot, cudaMemcpyDeviceToHost, h->d2h_stream));
+    CK(cudaEventRecord(sl.e_d2h, h->d2h_stream));
+    sl.busy = true;
+    return PILOTT_OK;
+}
+
+int pilott_mem_search_host_end(pilott_mem_t* h, int slot, int64_t* out_idx_host, float* out_score_host,
+                               double* out_score64_host, int32_t* n_fallback) {
+    if (!h) return fail(PILOTT_EINVAL, "handle is NULL");
+    if (slot < 0 || slot >= HOST_SLOTS) return fail(PILOTT_EINVAL, "slot must be in [0, 4)");
+    if (n_fallback) *n_fallback = 0;
+    HostSlot& sl = h->hslot[slot];
+    if (!sl.busy) return fail(PILOTT_EINVAL, "slot is not in flight");
+    if (!out_idx_host || !out_score_host) return fail(PILOTT_EINVAL, "NULL output pointer");
+    DeviceGuard g(h->device);
+    sl.busy = false;
+    CK(cudaEventSynchronize(sl.e_d2h));
+    char* rh = (char*)sl.res_host.p;
+    char* rd = (char*)sl.res_dev.p;
+    const int64_t nq = sl.nq;
+    const int k = sl.k;
+    if (!sl.fused) {
+        if (n_fallback) *n_fallback = (int32_t)nq;
+    } else if (*(int32_t*)(rh + sl.off_c) > 0) {
+        // second-chance pass for the flagged queries (brute force behind it), then the block again
+        cudaStream_t st = h->own_stream;
+        std::vector<int32_t> ids;
+        for (int64_t i = 0; i < nq; ++i) if (((uint8_t*)(rh + sl.off_f))[i]) ids.push_back((int32_t)i);
+        int rc = h->result_ids.ensure(ids.size() * 4);
+        if (rc) return rc;
+        CK(cudaMemcpyAsync(h->result_ids.p, ids.data(), ids.size() * 4, cudaMemcpyHostToDevice, st));
+        CK(cudaStreamSynchronize(st));
+        rc = refine_core(h, (const float*)sl.q_dev.p, nq, (const int32_t*)h->result_ids.p, (int64_t)ids.size(), k,
+                         sl.min_prio, sl.req, sl.now_us, (int64_t*)rd, (float*)(rd + sl.off_s),
+                         (double*)(rd + sl.off_s64), nullptr, st);
+        if (rc) return rc;
+        CK(cudaMemcpyAsync(rh, rd, sl.rtot, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        if (n_fallback) *n_fallback = (int32_t)ids.size();
+    }
+    memcpy(out_idx_host, rh, (size_t)nq * k * 8);
+    memcpy(out_score_host, rh + sl.off_s, (size_t)nq * k * 4);
+    if (out_score64_host) memcpy(out_score64_host, rh + sl.off_s64, (size_t)nq * k * 8);
     return PILOTT_OK;
 }
 

@@ -173,6 +173,32 @@ class SemanticStore:
                                           self._stream()))
         return idx, sc, sc64, inexact, flags
 
+    def search_host_begin(self, slot: int, q: np.ndarray, k: int, min_priority: int = 0, req_tagmask: int = 0,
+                          now_us: int = 0) -> None:
+        """First half of the pipelined host path (pilott_mem_search_host_begin): returns at once.
+        q: fp32 [nq, dim] numpy array; keep it alive (and unchanged) until search_host_end(slot)."""
+        q = np.ascontiguousarray(np.atleast_2d(q), dtype=np.float32)
+        if q.shape[1] != self.dim:
+            raise ValueError(f"expected queries of dim {self.dim}, got {q.shape[1]}")
+        check(self._lib.pilott_mem_search_host_begin(self._h, int(slot), ptr(q), q.shape[0], int(k), int(min_priority),
+                                                     int(req_tagmask), int(now_us)))
+        self._host_inflight = getattr(self, "_host_inflight", {})
+        self._host_inflight[slot] = (q, k)
+
+    def search_host_end(self, slot: int, want_score64: bool = False):
+        """Second half: waits for the slot, repairs flagged queries, returns numpy (idx, score[, score64])."""
+        if slot not in getattr(self, "_host_inflight", {}):
+            raise ValueError(f"slot {slot} is not in flight")
+        q, k = self._host_inflight.pop(slot)
+        nq = q.shape[0]
+        idx = np.empty((nq, k), np.int64)
+        sc = np.empty((nq, k), np.float32)
+        sc64 = np.empty((nq, k), np.float64) if want_score64 else None
+        nfb = C.c_int32()
+        check(self._lib.pilott_mem_search_host_end(self._h, int(slot), ptr(idx), ptr(sc), ptr(sc64), C.byref(nfb)))
+        self.last_fallbacks = nfb.value
+        return (idx, sc, sc64) if want_score64 else (idx, sc)
+
     def search_into(self, q, k, idx, sc, sc64, inexact, flags, min_priority=0, req_tagmask=0, now_us=0):
         """Device search writing into caller-owned tensors (no allocation in the hot loop)."""
         check(self._lib.pilott_mem_search(self._h, ptr(q), q.shape[0], int(k), int(min_priority),

@@ -144,3 +144,36 @@ def test_list_length_floor_rises_after_flagged_batches(torch_cuda):
     _same(idx, sc, sc64, os_, q, k)
     assert flagged[0] > 0 and flagged[-1] < flagged[0]
     gs.close()
+
+
+def test_pipelined_host_search_matches_oracle_and_repairs(torch_cuda):
+    """pilott_mem_search_host_begin / _end: three batches in flight at once (pageable numpy inputs),
+    one of them built to be flagged; slots are reusable and a busy slot is refused."""
+    from pilottai_b200._lib import PilottError
+    n, dim, k = 30000, 256, 10
+    x, topics = _bursty(n, dim, 12, seed=21, noise=0.02)
+    gs, os_ = _stores(x, 32768)
+    gs.set_list_len(8)
+    rng = np.random.default_rng(22)
+    near = lambda m: (topics[rng.integers(0, topics.shape[0], m)] + 0.02 * rng.standard_normal((m, dim))).astype(np.float32)
+    batches = [near(100), rng.standard_normal((64, dim)).astype(np.float32), near(33)]
+    for rep in range(2):                                   # second round reuses the slots
+        for s, q in enumerate(batches):
+            gs.search_host_begin(s, q, k)
+        outs, fallbacks = [], []
+        for s in range(3):
+            outs.append(gs.search_host_end(s, want_score64=True))
+            fallbacks.append(gs.last_fallbacks)
+        for q, (idx, sc, sc64) in zip(batches, outs):
+            _same(idx, sc, sc64, os_, q, k)
+        if rep == 0:
+            assert fallbacks[0] > 0 and fallbacks[2] > 0
+    gs.search_host_begin(0, batches[1], k)
+    with pytest.raises(PilottError):
+        gs.search_host_begin(0, batches[1], k)
+    with pytest.raises(ValueError):
+        gs.search_host_end(1)
+    idx, sc = gs.search_host_end(0)
+    sidx, ssc = gs.search(batches[1], k)
+    assert np.array_equal(idx, sidx) and np.array_equal(sc, ssc)
+    gs.close()
