@@ -244,14 +244,14 @@ def run_ours(args):
     else:
         h2d_s, d2h_s = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
         qdev = [torch.empty((NQ, DIM), dtype=torch.float32, device=dev) for _ in range(2)]
-        out_i = [torch.empty((NQ, TOPK), dtype=torch.int64).pin_memory() for _ in range(2)]
-        out_s = [torch.empty((NQ, TOPK), dtype=torch.float32).pin_memory() for _ in range(2)]
-        out_c = [torch.zeros(1, dtype=torch.int32).pin_memory() for _ in range(2)]
+        pack_bytes = NQ * TOPK * 12 + 8                  # merged idx int64 | score fp32 | inexact counter (sharded.py)
+        out_p = [torch.empty(pack_bytes, dtype=torch.uint8).pin_memory() for _ in range(2)]
+        out_c = [p[NQ * TOPK * 12: NQ * TOPK * 12 + 4].view(torch.int32) for p in out_p]
         ev_h2d = [torch.cuda.Event() for _ in range(2)]
         ev_used = [torch.cuda.Event() for _ in range(2)]
         ev_done = [torch.cuda.Event() for _ in range(2)]
         ev_d2h = [torch.cuda.Event() for _ in range(2)]
-        d2h = NQ * TOPK * (8 + 4) + 4
+        d2h = pack_bytes
 
         def e2e_run(n):
             main = torch.cuda.current_stream(dev)
@@ -260,13 +260,11 @@ def run_ours(args):
 
             def finish(j):
                 s = j % 2
-                m_idx, m_sc, _, cnt = store.search_end(tickets[s])
+                store.search_end(tickets[s])                         # merge into the slot's packed result block
                 ev_done[s].record(main)
                 d2h_s.wait_event(ev_done[s])
                 with torch.cuda.stream(d2h_s):
-                    out_i[s].copy_(m_idx, non_blocking=True)
-                    out_s[s].copy_(m_sc, non_blocking=True)
-                    out_c[s].copy_(cnt, non_blocking=True)
+                    out_p[s].copy_(tickets[s][0]["pack"], non_blocking=True)    # ONE D2H: indices, scores, counter
                 ev_d2h[s].record(d2h_s)
 
             for i in range(n):

@@ -80,14 +80,19 @@ class ShardedSemanticStore:
         key = (nq, k, slot)
         if key not in self._bufs:
             mine = torch.empty((2, nq, k), dtype=torch.int64, device=dev)          # [0] indices, [1] fp64 score bits
+            # merged results + the local inexact counter in ONE allocation, so that a host-side
+            # consumer fetches a batch with a single D2H copy: [idx int64 | score fp32 | counter int32 | pad]
+            ib, sb = nq * k * 8, nq * k * 4
+            pack = torch.zeros(ib + sb + 8, dtype=torch.uint8, device=dev)
             self._bufs[key] = {
                 "mine": mine, "idx": mine[0], "sc64": mine[1].view(torch.float64),
                 "sc": torch.empty((nq, k), dtype=torch.float32, device=dev),
                 "flags": torch.empty(nq, dtype=torch.uint8, device=dev),
-                "inexact": torch.zeros(1, dtype=torch.int32, device=dev),
+                "pack": pack,
+                "inexact": pack[ib + sb: ib + sb + 4].view(torch.int32),
                 "gathered": torch.empty((self.world, 2, nq, k), dtype=torch.int64, device=dev),
-                "m_idx": torch.empty((nq, k), dtype=torch.int64, device=dev),
-                "m_sc": torch.empty((nq, k), dtype=torch.float32, device=dev),
+                "m_idx": pack[:ib].view(torch.int64).view(nq, k),
+                "m_sc": pack[ib: ib + sb].view(torch.float32).view(nq, k),
                 "m_sc64": torch.empty((nq, k), dtype=torch.float64, device=dev),
             }
         return self._bufs[key]
