@@ -54,6 +54,7 @@ class ShardedSemanticStore:
             raise ValueError("exchange must be 'auto', 'p2p' or 'nccl'")
         self.exchange = exchange if world > 1 else "none"
         self._xchg = {}                                 # (nq, k) -> [handle, next step]
+        self._ridx = {}                                 # cached row-selection indices for device appends
         self.local = SemanticStore(dim, (capacity + world - 1) // world, device)
         self.local.set_sequence_map(world, rank)
         self.dim, self.device = dim, device
@@ -70,7 +71,10 @@ class ShardedSemanticStore:
             if isinstance(x, np.ndarray):
                 sel = lambda a: None if a is None else np.ascontiguousarray(a[rows])
             else:
-                ridx = torch.from_numpy(rows).to(x.device)
+                key = (int(rows[0]), n, x.device)                 # the pattern only depends on first % world and n
+                ridx = self._ridx.get(key)
+                if ridx is None:
+                    ridx = self._ridx[key] = torch.from_numpy(rows).to(x.device)
                 sel = lambda a: None if a is None else a.index_select(0, ridx)
             self.local.append(sel(x), sel(prio), sel(tagmask), sel(expires_us))
         self.total += n
