@@ -291,6 +291,19 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
     const int64_t q0 = ((int64_t)group * CG + rank) * BM;               // this CTA's first query row
     const int64_t ntiles = (nslots + BN - 1) / BN;
     const int64_t t_lo = ntiles * slot / slots_g, t_hi = ntiles * (slot + 1) / slots_g;
+    // Pair mode with at most 128 real queries in the group (single queries, small or ragged
+    // batches): the second CTA's whole query tile is padding.  It zeroes its A stages once and never
+    // loads them again -- a quarter less L2 -> SM traffic in the regime where that traffic is the
+    // bound -- and its epilogue warps only hand the accumulator back.
+    const bool a_pad = CG == 2 && q0 >= nq;                              // this CTA's tile has no query
+    const bool pair_pad = CG == 2 && ((int64_t)group * CG + 1) * BM >= nq;   // ... the pair's second tile
+    if (a_pad) {
+        for (int st = 0; st < Cfg::STAGES; ++st) {
+            uint4* a = reinterpret_cast<uint4*>(base_ptr + st * Cfg::STAGE_BYTES);
+            for (int i = threadIdx.x; i < Cfg::A_BYTES / 16; i += TC_THREADS) a[i] = make_uint4(0, 0, 0, 0);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic stores -> visible to UMMA
+    }
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_q) : "memory");
@@ -346,8 +359,9 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                         // dbg & 64: traffic experiment -- skip the corpus (B) load on odd k-blocks (stale
                         // data, wrong results) to see how much of the mainloop time is L2 -> SM supply
                         const bool skip_b = (dbg & 64) && (kb & 1);
-                        if (leader) mbar_arrive_expect_tx(bar_full + 8 * stage, skip_b ? 2 * Cfg::A_BYTES : 2 * Cfg::STAGE_BYTES);
-                        tma_load_2d_cg2(sa, &map_q, kb * BK, (int)q0, full0 + 8 * stage);
+                        if (leader) mbar_arrive_expect_tx(bar_full + 8 * stage, (skip_b ? 2 * Cfg::A_BYTES : 2 * Cfg::STAGE_BYTES) -
+                                                                                      (pair_pad ? Cfg::A_BYTES : 0));
+                        if (!a_pad) tma_load_2d_cg2(sa, &map_q, kb * BK, (int)q0, full0 + 8 * stage);
                         if (!skip_b) tma_load_2d_cg2(sb, &map_c, kb * BK, n0, full0 + 8 * stage);
                     }
                     if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
@@ -443,7 +457,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
             // maxima published by the other CTAs sweeping the same query is a valid lower bound of
             // the query's global krank-th best (krank distinct rows reach it), so it becomes the initial
             // threshold; pass B is the normal scan of the same (still resident) accumulator tile.
-            if (ti == 0 && cold && !(dbg & 1)) {
+            if (ti == 0 && cold && !(dbg & 1) && !a_pad) {
                 float rowmax = -INFINITY;
 #pragma unroll 1
                 for (int c = set * CPS; c < (set + 1) * CPS; c += 16) {
@@ -552,7 +566,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
             // Software pipeline over the set's 128 columns: the TMEM load of the next chunk is in
             // flight while the current one is processed (two register buffers, ping-pong).
             const long long cl = (dbg & 4) ? clock64() : 0;
-            if (!(dbg & 1)) {
+            if (!(dbg & 1) && !a_pad) {
                 uint32_t va[16], vb[16];
                 const int c_lo = set * CPS, c_hi = (set + 1) * CPS;
                 tmem_ld16_issue(taddr0 + c_lo, va);
