@@ -221,3 +221,30 @@ def test_serve_adapter_wires_router_and_memory(torch_cuda, golden_dir):
         assert hit[0].metadata["task_id"] == "t-1" and hit[0].priority == 1
         mem.close()
     asyncio.run(scenario())
+
+
+@pytest.mark.parametrize("name", ["small", "mid"])
+def test_enhanced_memory_dropin_returns_the_reference_lists(torch_cuda, golden_dir, name):
+    """tests/golden/memory_filters.json holds what the UNMODIFIED reference returned (every text
+    matches its substring test).  The drop-in gets the same items with one and the same embedding,
+    so every cosine ties and its answer is decided by the same rules alone: priority floor, tag
+    AND, expiry, (-priority, timestamp) order.  `small` (28 items, limit 32) goes through the fused
+    path and its repair step (all scores tie), `mid` (60 items, limit 100) through the large-k path."""
+    from pilottai_b200.memory import EnhancedMemory
+    with open(os.path.join(golden_dir, "memory_filters.json")) as f:
+        sc = json.load(f)[name]
+    limit = 32 if name == "small" else 100
+    e = np.ones(64, np.float32)
+
+    async def run():
+        mem = EnhancedMemory(max_size=10000, dim=64)
+        for it in sc["items"]:
+            await mem.store_semantic(it["text"], tags=set(it["tags"]), priority=it["priority"], ttl=it["ttl"], embedding=e)
+            await asyncio.sleep(0.0003)                        # distinct timestamps, as in the fixture run
+        await asyncio.sleep(0.01)
+        for q in sc["queries"]:
+            got = await mem.semantic_search("needle", tags=set(q["tags"]) or None, min_priority=q["min_priority"],
+                                            limit=limit, query_embedding=e)
+            assert [g.text for g in got] == q["expect"], q
+        mem.close()
+    asyncio.run(run())
