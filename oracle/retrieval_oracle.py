@@ -16,6 +16,12 @@ reference DOES specify is followed here and cited line by line:
 * older-first ordering among equals (stable sort on timestamp)
                                              -> enhanced_memory.py:114
 
+Those candidate rules ARE pinned on the reference itself: oracle/gen_golden_memory.py runs the
+unmodified reference on texts that all match the query and commits the lists it returns
+(tests/golden/memory_filters.json); tests/test_oracle_memory_filters.py holds `valid_mask` and the
+tie order of this file to them.  Only the scoring rule below has nothing in the reference to be
+checked against.
+
 THE STATED SCORING RULE (this build's definition, the GPU must reproduce it):
 
 1. Vectors are rounded fp32 -> bf16, round-to-nearest-even (NaN -> 0x7FFF).
