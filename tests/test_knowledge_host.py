@@ -70,3 +70,17 @@ def test_lru_eviction_ttl_and_retry(monkeypatch):
         assert await km.query_knowledge("z", ["flaky"]) == [{"q": "z", "n": 3}]
         assert slept == [7, 7] and src.error_count == 2
     asyncio.run(go())
+
+
+def test_scripted_session_matches_the_reference_log(golden_dir):
+    """tests/golden/knowledge_session.json is the log of oracle/knowledge_script.py run against the
+    UNMODIFIED reference KnowledgeManager (oracle/gen_golden_knowledge.py); the drop-in must produce
+    the same log: return values, cache keys in LRU order, per-source counters, error strings."""
+    import os
+    from oracle.knowledge_script import session
+    with open(os.path.join(golden_dir, "knowledge_session.json")) as f:
+        want = json.load(f)
+    got = json.loads(json.dumps(asyncio.run(session(KnowledgeManager, KnowledgeSource))))
+    assert len(got) == len(want)
+    for g, w in zip(got, want):
+        assert g == w, (g, w)
