@@ -288,22 +288,33 @@ class LoadBalancer:
             try:
                 tasks = await self._get_moveable_tasks(over_id)
                 tasks.sort(key=lambda x: x.get("priority", 0), reverse=True)
-                tasks = tasks[: self.config.balance_batch_size * 4]
-                targets = await self._find_best_agents(tasks, underloaded, current_metrics)
-                moves = 0
-                for task, best in zip(tasks, targets):
-                    if moves >= self.config.balance_batch_size:
-                        break
-                    if not best:
-                        continue
-                    try:
-                        async with asyncio.timeout(self.config.task_move_timeout):
-                            await self._move_task(task, over_id, best)
-                            moves += 1
-                    except asyncio.TimeoutError:
-                        self.logger.error(f"Task move timed out for task {task['id']}")
-                    except Exception as e:
-                        self.logger.error(f"Failed to move task {task['id']}: {str(e)}")
+                # The reference scores one task at a time (:192-213), and a move changes the target's
+                # queue (agent.tasks grows), which the next task's base suitability sees
+                # (agent.py:566-571).  So: score the tasks still to be placed in one device batch
+                # against the current agent state, walk them in order up to the first successful
+                # move, then re-snapshot and re-score what is left.  At most balance_batch_size + 1
+                # device calls per overloaded agent, same assignments as the one-by-one loop.
+                moves, pos = 0, 0
+                chunk = max(1, self.config.balance_batch_size * 4)
+                while pos < len(tasks) and moves < self.config.balance_batch_size:
+                    part = tasks[pos: pos + chunk]
+                    targets = await self._find_best_agents(part, underloaded, current_metrics)
+                    moved = False
+                    for task, best in zip(part, targets):
+                        pos += 1
+                        if not best:
+                            continue
+                        try:
+                            async with asyncio.timeout(self.config.task_move_timeout):
+                                await self._move_task(task, over_id, best)
+                                moves += 1
+                                moved = True
+                        except asyncio.TimeoutError:
+                            self.logger.error(f"Task move timed out for task {task['id']}")
+                        except Exception as e:
+                            self.logger.error(f"Failed to move task {task['id']}: {str(e)}")
+                        if moved:
+                            break                                   # agent state changed: re-score the rest
                 if moves > 0:
                     self._last_balance_time = datetime.now()
             except Exception as e:

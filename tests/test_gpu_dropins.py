@@ -248,3 +248,46 @@ def test_enhanced_memory_dropin_returns_the_reference_lists(torch_cuda, golden_d
             assert [g.text for g in got] == q["expect"], q
         mem.close()
     asyncio.run(run())
+
+
+def test_load_balancer_redistribution_matches_reference(torch_cuda, golden_dir):
+    """tests/golden/rebalance.json: which tasks the UNMODIFIED reference's _redistribute_tasks
+    (load_balancer.py:180-266) moved off three overloaded agents, and where to.  A move grows the
+    target's queue and the next task's base suitability sees it (agent.py:566-571), so the
+    batched drop-in has to re-score after every move to land on the same assignments."""
+    import copy
+    from pilottai_b200 import LoadBalancer, LoadMetrics
+    with open(os.path.join(golden_dir, "rebalance.json")) as f:
+        g = json.load(f)
+
+    class DictTaskAgent(FakeAgent):
+        def __init__(self, row, queue):
+            super().__init__(row)
+            own = [{"id": f"{row['id']}-own{j}", "status": "running"} for j in range(row["queue_size"])]
+            self.tasks = {t["id"]: t for t in copy.deepcopy(queue if queue is not None else own)}
+
+        async def get_metrics(self):
+            return ro.agent_metrics(dict(self.row, queue_size=len(self.tasks)))     # agent.py:535-547
+
+        async def add_task(self, task):
+            if task["id"] in self.tasks:
+                raise ValueError(f"Task {task['id']} already exists")
+            self.tasks[task["id"]] = task
+
+        async def remove_task(self, task_id):
+            self.tasks.pop(task_id, None)
+
+    kids = {r["id"]: DictTaskAgent(r, g["queues"].get(r["id"])) for r in g["agents"]}
+
+    class Orch:
+        child_agents = kids
+        verbose = False
+    orch = Orch()                                          # the balancer keeps a weak reference, like the reference
+    lb = LoadBalancer(orch, g["lb_config"])
+    metrics = {r["id"]: LoadMetrics(**ro.lb_metrics(r, g["system_cpu_percent"], g["system_mem_percent"]))
+               for r in g["agents"]}
+    asyncio.run(lb._redistribute_tasks(list(g["overloaded"]), list(g["underloaded"]), metrics))
+    moved = sorted(({"task": t["id"], "from": t["moved_from"], "to": t["moved_to"]}
+                    for a in kids.values() for t in a.tasks.values() if "moved_to" in t), key=lambda m: m["task"])
+    assert moved == g["result"]["moved"]
+    assert {aid: list(a.tasks.keys()) for aid, a in kids.items()} == g["result"]["queues_after"]
