@@ -115,7 +115,10 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": v, "unit": "queries/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
-        "data": "synthetic", "config": {"workload": WORKLOAD, "step": f"{sample_q}-query sample of a batch, full corpus"},
+        "data": "synthetic",
+        "config": {"workload": WORKLOAD, "rows": N_ROWS, "dim": DIM, "queries_per_step": NQ, "k": TOPK,
+                   "sharding": "host cores (rank 0 only)",
+                   "step": f"{sample_q}-query sample of a {NQ}-query batch against the full corpus"},
         "cpu_baseline": {"value": v, "unit": "queries/s", "cores": cores, "kind": "port",
                          "sample": f"{sample_q} queries/step x {args.steps} steps against all {N_ROWS} rows (numpy BLAS fp32 + argpartition)"},
         "e2e": {"value": v, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
