@@ -30,6 +30,8 @@ extern "C" {
 /* Largest k the fused similarity + top-k path answers; larger k (and queries the
  * fused path flags as not provably exact) go through pilott_mem_search_exact. */
 #define PILOTT_MAX_FUSED_K 32
+/* Largest k the threshold-collect path answers (pilott_mem_search_large); beyond it: brute force. */
+#define PILOTT_MAX_LARGE_K 1024
 /* Tags are stored as one 64-bit mask per row. */
 #define PILOTT_MAX_TAGS 64
 
@@ -121,6 +123,19 @@ int pilott_mem_search_host_begin(pilott_mem_t* h, int slot, const float* q_host,
                                  int32_t min_prio, uint64_t req_tagmask, int64_t now_us);
 int pilott_mem_search_host_end(pilott_mem_t* h, int slot, int64_t* out_idx_host, float* out_score_host,
                                double* out_score64_host, int32_t* n_fallback);
+/* Top-k for PILOTT_MAX_FUSED_K < k <= PILOTT_MAX_LARGE_K without scoring every row in fp64 (any
+ * other k is handed to the fused or the brute-force path).  The fused top-32 of each query gives
+ * two points of its score tail; a per-query threshold extrapolated to rank ~1.5k is applied by the
+ * tensor-core scan in COLLECT mode; the collected rows are re-scored by the stated rule, ranked,
+ * and the guess is CHECKED (the k-th exact score must clear every row that was not collected);
+ * queries whose guess was too high (or collected more than 4096 rows) repeat with a guess refitted
+ * from the row count the pass measured, at most twice, then with an open threshold.  Same results as pilott_mem_search_exact, bit for bit.  *n_bruteforce (host, may
+ * be NULL): queries that ended in the brute-force kernels (more than 4096 rows above their
+ * threshold).  Synchronises `stream` between passes.  The host-buffer entry points use this path
+ * for k > PILOTT_MAX_FUSED_K.  No counterpart in the reference. */
+int pilott_mem_search_large(pilott_mem_t* h, const float* q_dev, int64_t nq, int k, int32_t min_prio,
+                            uint64_t req_tagmask, int64_t now_us, int64_t* out_idx_dev, float* out_score_dev,
+                            double* out_score64_dev, int32_t* n_bruteforce, void* stream);
 /* Brute-force fp64 search (any k >= 1): every candidate row scored in the oracle's order.
  * Slow path for flagged queries / large k.  query_ids_dev (int32[nsel], may be NULL = all
  * nq) selects which rows of q/out to process. */

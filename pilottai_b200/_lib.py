@@ -39,6 +39,8 @@ SIGNATURES = {
                                          c_vp, C.POINTER(c_i32)]),
     "pilott_mem_search_host_begin": (C.c_int, [c_vp, C.c_int, c_vp, c_i64, C.c_int, c_i32, c_u64, c_i64]),
     "pilott_mem_search_host_end": (C.c_int, [c_vp, C.c_int, c_vp, c_vp, c_vp, C.POINTER(c_i32)]),
+    "pilott_mem_search_large": (C.c_int, [c_vp, c_vp, c_i64, C.c_int, c_i32, c_u64, c_i64, c_vp, c_vp, c_vp,
+                                          C.POINTER(c_i32), c_vp]),
     "pilott_mem_search_exact": (C.c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, C.c_int, c_i32, c_u64, c_i64,
                                           c_vp, c_vp, c_vp, c_vp]),
     "pilott_mem_search_refine": (C.c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, C.c_int, c_i32, c_u64, c_i64,

@@ -5,6 +5,7 @@
 #include <cudaTypedefs.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -123,6 +124,7 @@ struct HostSlot {
     uint64_t req = 0;
     int64_t now_us = 0;
     bool busy = false, fused = true;
+    int32_t n_brute = 0;       // large k: queries that went to the brute-force kernels
     size_t off_s64 = 0, off_s = 0, off_f = 0, off_c = 0, rtot = 0;
 };
 constexpr int HOST_SLOTS = 4;
@@ -140,7 +142,7 @@ struct pilott_mem {
     int64_t* expires = nullptr;
     float* scale = nullptr;
     float* tile_max = nullptr;
-    DevBuf qbuf, partials, gthr, exact_scratch, stage_dev, result_dev, misc_dev, refine, result_ids;
+    DevBuf qbuf, partials, gthr, exact_scratch, stage_dev, result_dev, misc_dev, refine, result_ids, largek;
     HostBuf stage_host;
     cudaStream_t own_stream = nullptr;
     cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;   // copy streams of the pipelined host path
@@ -427,7 +429,7 @@ int refine_core(pilott_mem* h, const float* q_dev, int64_t nq, const int32_t* qi
     CK(pilott::launch_scan_tc(a, &map_q, &map_c, 2, ctas, st));
     CK(pilott::launch_refine_finish(cand, cnt, REFINE_CAP, qb2, h->vec, h->ld, qids, nsel, h->capacity, h->head,
                                     h->total - h->count, h->seq_mul, h->seq_add, k, out_idx, out_score, out_score64,
-                                    ovf, n_ovf, st));
+                                    ovf, n_ovf, nullptr, err, nullptr, nullptr, st));
     h->launches += 4;
     int32_t novf = 0;
     CK(cudaMemcpyAsync(&novf, n_ovf, 4, cudaMemcpyDeviceToHost, st));
@@ -446,6 +448,118 @@ int refine_core(pilott_mem* h, const float* q_dev, int64_t nq, const int32_t* qi
         CK(cudaStreamSynchronize(st));
         if (n_brute) *n_brute = (int32_t)over.size();
         return exact_core(h, q_dev, nq, (const int32_t*)h->misc_dev.p, (int64_t)over.size(), k, min_prio, req, now_us,
+                          out_idx, out_score, out_score64, st);
+    }
+    return PILOTT_OK;
+}
+
+// Large k (PILOTT_MAX_FUSED_K < k <= PILOTT_MAX_LARGE_K): fused top-32 first (it supplies s_4 and
+// s_32 of every query), then COLLECT passes whose per-query thresholds are extrapolated guesses at
+// rank 1.5k (refitted from the row count each pass measures) and finally an open threshold; refine_finish_kernel re-scores what a pass
+// collected, ranks it and checks the guess (the k-th exact score must clear every uncollected
+// row); queries whose guess was too high go into the next pass, queries with more than
+// LARGEK_CAP collected rows and whatever is left after the last pass go to brute force.
+// Synchronises the stream between passes.
+constexpr int LARGEK_CAP = 4096;
+
+int largek_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t min_prio, uint64_t req,
+                int64_t now_us, int64_t* out_idx, float* out_score, double* out_score64, int32_t* n_brute,
+                cudaStream_t st) {
+    if (n_brute) *n_brute = 0;
+    if (nq <= 0) return PILOTT_OK;
+    if (k <= PILOTT_MAX_FUSED_K || k > PILOTT_MAX_LARGE_K || pick_kernel(h) != 3 || h->count == 0) {
+        if (n_brute) *n_brute = (int32_t)nq;
+        return exact_core(h, q_dev, nq, nullptr, nq, k, min_prio, req, now_us, out_idx, out_score, out_score64, st);
+    }
+    // 1. fused top-32 into scratch (prepare inside it converts the queries and builds the filter mask)
+    const size_t t_idx_b = (size_t)nq * 32 * 8, t_s_b = (size_t)nq * 32 * 4;
+    const size_t fl_b = (size_t)round_up(nq, 8);
+    int rc = h->largek.ensure(2 * t_idx_b + t_s_b + fl_b + 16 + (size_t)nq * 12);
+    if (rc) return rc;
+    char* tb = (char*)h->largek.p;
+    int64_t* top_idx = (int64_t*)tb;
+    double* top_s64 = (double*)(tb + t_idx_b);
+    float* top_s = (float*)(tb + 2 * t_idx_b);
+    uint8_t* top_flags = (uint8_t*)(tb + 2 * t_idx_b + t_s_b);
+    int32_t* top_cnt = (int32_t*)(tb + 2 * t_idx_b + t_s_b + fl_b);
+    double* hist_t = (double*)(tb + 2 * t_idx_b + t_s_b + fl_b + 16);       // per query: last threshold tried ...
+    uint32_t* hist_c = (uint32_t*)(hist_t + nq);                            // ... and how many rows lay above it
+    CK(cudaMemsetAsync(hist_t, 0, (size_t)nq * 12, st));
+    rc = search_core(h, q_dev, nq, PILOTT_MAX_FUSED_K, min_prio, req, now_us, top_idx, top_s, top_s64, top_cnt, top_flags, st);
+    if (rc) return rc;
+
+    // 2. passes over the queries still open
+    const double err = h->ld * 2.4e-7 > 1e-4 ? h->ld * 2.4e-7 : 1e-4;
+    std::vector<int32_t> open_ids((size_t)nq), brute;
+    for (int64_t i = 0; i < nq; ++i) open_ids[i] = (int32_t)i;
+    const double factors[4] = {1.5, 1.5, 2.0, 0.0};       // target ranks as multiples of k; 0 = open threshold
+    const int ctas = h->opt_ctas > 0 ? h->opt_ctas : h->num_sms;
+    CUtensorMap map_q, map_c;
+    rc = encode_map(&map_c, h->vec, h->capacity, h->ld, 128);
+    if (rc) return rc;
+    for (int pass = 0; pass < 4 && !open_ids.empty(); ++pass) {
+        const int64_t nsel = (int64_t)open_ids.size(), nsel_pad = round_up(nsel, 256);
+        const size_t qb2_b = (size_t)nsel_pad * h->ld * 2, w_b = (size_t)nsel_pad * 4, d_b = (size_t)nsel_pad * 8;
+        const size_t cand_b = (size_t)nsel * LARGEK_CAP * 4, ovf_b = (size_t)round_up(nsel, 8), ids_b = (size_t)round_up(nsel * 4, 8);
+        rc = h->refine.ensure(qb2_b + 2 * w_b + d_b + cand_b + ovf_b + ids_b + 8);
+        if (rc) return rc;
+        char* base = (char*)h->refine.p;
+        void* qb2 = base;
+        uint32_t* thr_bits = (uint32_t*)(base + qb2_b);
+        uint32_t* cnt = (uint32_t*)(base + qb2_b + w_b);
+        double* tcos = (double*)(base + qb2_b + 2 * w_b);
+        uint32_t* cand = (uint32_t*)(base + qb2_b + 2 * w_b + d_b);
+        uint8_t* status = (uint8_t*)(base + qb2_b + 2 * w_b + d_b + cand_b);
+        int32_t* ids_dev = (int32_t*)(base + qb2_b + 2 * w_b + d_b + cand_b + ovf_b);
+        int32_t* n_open = (int32_t*)(base + qb2_b + 2 * w_b + d_b + cand_b + ovf_b + ids_b);
+        CK(cudaMemcpyAsync(ids_dev, open_ids.data(), (size_t)nsel * 4, cudaMemcpyHostToDevice, st));
+        CK(pilott::launch_largek_prepare(h->qbuf.p, ids_dev, nsel, nsel_pad, h->ld, top_idx, top_s64, k, factors[pass],
+                                         8.0 * err * (pass + 1), (double)h->count, hist_t, hist_c, (double)LARGEK_CAP, qb2, thr_bits, tcos,
+                                         cnt, n_open, st));
+        pilott::ScanArgs a{};
+        a.qb = qb2; a.vec = h->vec; a.scale = h->scale; a.tile_max = h->tile_max; a.nq = nsel;
+        a.nslots = h->count; a.capacity = h->capacity; a.head = h->head; a.ld = h->ld;
+        a.partials = (uint64_t*)cand; a.gthr = thr_bits; a.gmax = cnt; a.collect_cap = LARGEK_CAP;
+        a.list_len = 8; a.krank = 16; a.dbg = 0;
+        a.slots = pilott::scan_tc_slots(nsel, h->count, 2, ctas, &a.slots_rem);
+        rc = encode_map(&map_q, qb2, nsel_pad, h->ld, 128);
+        if (rc) return rc;
+        CK(pilott::launch_scan_tc(a, &map_q, &map_c, 2, ctas, st));
+        CK(pilott::launch_refine_finish(cand, cnt, LARGEK_CAP, qb2, h->vec, h->ld, ids_dev, nsel, h->capacity, h->head,
+                                        h->total - h->count, h->seq_mul, h->seq_add, k, out_idx, out_score, out_score64,
+                                        status, n_open, tcos, err, hist_t, hist_c, st));
+        h->launches += 3;
+        int32_t nopen = 0;
+        CK(cudaMemcpyAsync(&nopen, n_open, 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        if (nopen == 0) { open_ids.clear(); break; }
+        std::vector<uint8_t> stt((size_t)nsel);
+        CK(cudaMemcpyAsync(stt.data(), status, (size_t)nsel, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        std::vector<int32_t> next;
+        if (getenv("PILOTT_DEBUG_LARGEK")) {
+            std::vector<uint32_t> cc((size_t)nsel);
+            std::vector<double> tt((size_t)nsel);
+            cudaMemcpy(cc.data(), cnt, (size_t)nsel * 4, cudaMemcpyDeviceToHost);
+            cudaMemcpy(tt.data(), tcos, (size_t)nsel * 8, cudaMemcpyDeviceToHost);
+            int shown = 0;
+            for (int64_t i = 0; i < nsel && shown < 6; ++i)
+                if (stt[i]) { fprintf(stderr, "[largek pass %d] query %d status %d rows %u threshold %.6f\n", pass, open_ids[i], (int)stt[i], cc[i], tt[i]); ++shown; }
+            fprintf(stderr, "[largek pass %d] %d of %lld still open\n", pass, nopen, (long long)nsel);
+        }
+        for (int64_t i = 0; i < nsel; ++i) {
+            if (stt[i] != 0 && pass < 3) next.push_back(open_ids[i]);          // guess too high or too low: refit, retry
+            else if (stt[i] != 0) brute.push_back(open_ids[i]);                // out of passes
+        }
+        open_ids.swap(next);
+    }
+    if (!brute.empty()) {
+        rc = h->misc_dev.ensure(brute.size() * 4);
+        if (rc) return rc;
+        CK(cudaMemcpyAsync(h->misc_dev.p, brute.data(), brute.size() * 4, cudaMemcpyHostToDevice, st));
+        CK(cudaStreamSynchronize(st));
+        if (n_brute) *n_brute = (int32_t)brute.size();
+        return exact_core(h, q_dev, nq, (const int32_t*)h->misc_dev.p, (int64_t)brute.size(), k, min_prio, req, now_us,
                           out_idx, out_score, out_score64, st);
     }
     return PILOTT_OK;
@@ -497,7 +611,7 @@ int pilott_mem_destroy(pilott_mem_t* h) {
     cudaDeviceSynchronize();
     free_columns(h);
     h->qbuf.release(); h->partials.release(); h->gthr.release(); h->exact_scratch.release(); h->stage_dev.release();
-    h->result_dev.release(); h->misc_dev.release(); h->refine.release(); h->result_ids.release();
+    h->result_dev.release(); h->misc_dev.release(); h->refine.release(); h->result_ids.release(); h->largek.release();
     h->stage_host.release();
     for (cudaEvent_t e : h->ev) cudaEventDestroy(e);
     for (auto& sl : h->hslot) {
@@ -670,6 +784,18 @@ int pilott_mem_search_refine(pilott_mem_t* h, const float* q_dev, int64_t nq, co
                        out_score_dev, out_score64_dev, n_bruteforce, (cudaStream_t)stream);
 }
 
+int pilott_mem_search_large(pilott_mem_t* h, const float* q_dev, int64_t nq, int k, int32_t min_prio,
+                            uint64_t req_tagmask, int64_t now_us, int64_t* out_idx_dev, float* out_score_dev,
+                            double* out_score64_dev, int32_t* n_bruteforce, void* stream) {
+    if (!h) return fail(PILOTT_EINVAL, "handle is NULL");
+    if (nq < 0) return fail(PILOTT_EINVAL, "nq is negative");
+    if (k < 1) return fail(PILOTT_EINVAL, "k must be >= 1");
+    if (nq > 0 && (!q_dev || !out_idx_dev || !out_score_dev)) return fail(PILOTT_EINVAL, "NULL query or output pointer");
+    DeviceGuard g(h->device);
+    return largek_core(h, q_dev, nq, k, min_prio, req_tagmask, now_us, out_idx_dev, out_score_dev, out_score64_dev,
+                       n_bruteforce, (cudaStream_t)stream);
+}
+
 int pilott_mem_search_host(pilott_mem_t* h, const float* q_host, int64_t nq, int k, int32_t min_prio,
                            uint64_t req_tagmask, int64_t now_us, int64_t* out_idx_host,
                            float* out_score_host, double* out_score64_host, int32_t* n_fallback) {
@@ -709,8 +835,9 @@ int pilott_mem_search_host(pilott_mem_t* h, const float* q_host, int64_t nq, int
     if (fused) {
         rc = search_core(h, qd, nq, k, min_prio, req_tagmask, now_us, d_idx, d_s, d_s64, d_c, d_f, st);
     } else {
-        rc = exact_core(h, qd, nq, nullptr, nq, k, min_prio, req_tagmask, now_us, d_idx, d_s, d_s64, st);
-        if (n_fallback) *n_fallback = (int32_t)nq;
+        int32_t nb = 0;
+        rc = largek_core(h, qd, nq, k, min_prio, req_tagmask, now_us, d_idx, d_s, d_s64, &nb, st);
+        if (n_fallback) *n_fallback = nb;      // queries that needed the brute-force kernels
     }
     if (rc) return rc;
     char* rh = (char*)h->stage_host.p;
@@ -784,8 +911,8 @@ int pilott_mem_search_host_begin(pilott_mem_t* h, int slot, const float* q_host,
                          (float*)(rd + sl.off_s), (double*)(rd + sl.off_s64), (int32_t*)(rd + sl.off_c),
                          (uint8_t*)(rd + sl.off_f), st);
     else
-        rc = exact_core(h, (const float*)sl.q_dev.p, nq, nullptr, nq, k, min_prio, req_tagmask, now_us, (int64_t*)rd,
-                        (float*)(rd + sl.off_s), (double*)(rd + sl.off_s64), st);
+        rc = largek_core(h, (const float*)sl.q_dev.p, nq, k, min_prio, req_tagmask, now_us, (int64_t*)rd,
+                         (float*)(rd + sl.off_s), (double*)(rd + sl.off_s64), &sl.n_brute, st);
     if (rc) return rc;
     CK(cudaEventRecord(sl.e_done, st));
     CK(cudaStreamWaitEvent(h->d2h_stream, sl.e_done, 0));
@@ -811,7 +938,7 @@ int pilott_mem_search_host_end(pilott_mem_t* h, int slot, int64_t* out_idx_host,
     const int64_t nq = sl.nq;
     const int k = sl.k;
     if (!sl.fused) {
-        if (n_fallback) *n_fallback = (int32_t)nq;
+        if (n_fallback) *n_fallback = sl.n_brute;
     } else if (*(int32_t*)(rh + sl.off_c) > 0) {
         // second-chance pass for the flagged queries (brute force behind it), then the block again
         cudaStream_t st = h->own_stream;

@@ -518,18 +518,25 @@ refine_finish_kernel(const uint32_t* __restrict__ cand, const uint32_t* __restri
                      const int32_t* __restrict__ qids, int64_t capacity, int64_t head, int64_t base_seq,
                      int64_t seq_mul, int64_t seq_add, int k, int64_t* __restrict__ out_idx,
                      float* __restrict__ out_score, double* __restrict__ out_score64,
-                     uint8_t* __restrict__ overflow, int32_t* __restrict__ n_overflow) {
+                     uint8_t* __restrict__ overflow, int32_t* __restrict__ n_overflow,
+                     const double* __restrict__ tcos, double err, double* __restrict__ hist_t,
+                     uint32_t* __restrict__ hist_c) {
+    // status written to overflow[sel]: 0 settled, 1 more candidates than `cap`, 2 (only with tcos: the
+    // large-k pass, whose thresholds are guesses) the k-th exact score is not provably above
+    // every uncollected row -- the threshold was too high, try a lower one.
     extern __shared__ __align__(16) unsigned char sm_raw[];
+    __shared__ double s_ek;
     double* s_sc = reinterpret_cast<double*>(sm_raw);                  // [cap]
     int64_t* s_age = reinterpret_cast<int64_t*>(s_sc + cap);           // [cap]
     const int64_t sel = blockIdx.x;
     const int64_t q = qids[sel];
     const uint32_t c = cnt[sel];
+    if (hist_t && threadIdx.x == 0) { hist_t[q] = tcos[sel]; hist_c[q] = c; }      // (threshold, rows above it): one measured point of the tail
     if (c > (uint32_t)cap) {                           // too many near-ties: brute force decides
         if (threadIdx.x == 0) { overflow[sel] = 1; atomicAdd(n_overflow, 1); }
         return;
     }
-    if (threadIdx.x == 0) overflow[sel] = 0;
+    if (threadIdx.x == 0) { overflow[sel] = 0; s_ek = -INFINITY; }
     const __nv_bfloat16* qrow = qb2 + sel * ld;
     for (uint32_t i = threadIdx.x; i < c; i += REFINE_THREADS) {
         const int64_t slot = cand[sel * cap + i];
@@ -555,6 +562,90 @@ refine_finish_kernel(const uint32_t* __restrict__ cand, const uint32_t* __restri
             out_score[q * k + rank] = (float)ms;
             if (out_score64) out_score64[q * k + rank] = ms;
         }
+        if (rank == k - 1) s_ek = ms;
+    }
+    if (tcos) {
+        // rows the scan did not collect have approximate cosine < tcos[sel], hence exact < tcos + err
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const double t = tcos[sel];
+            const bool all_rows = t == -INFINITY;      // open threshold: every candidate row was collected
+            if (!all_rows && !(c >= (uint32_t)k && s_ek >= t + err)) { overflow[sel] = 2; atomicAdd(n_overflow, 1); }
+        }
+    }
+}
+
+// Large k (32 < k <= 1024): no candidate lists that long exist, so the threshold of the COLLECT
+// pass is a GUESS -- the fused top-32 of the query gives s_4 and s_32; with the scores of the
+// n_rows held rows taken as normal, those two order statistics fix mean and spread, and the guess
+// is the score expected at rank factor * k -- and refine_finish_kernel CHECKS it (status 2 = too
+// high).  factor <= 0, a target rank beyond the store, or a tiny store open the threshold.
+__global__ void __launch_bounds__(128)
+largek_prepare_kernel(const __nv_bfloat16* __restrict__ qb, const int32_t* __restrict__ qids, int64_t nsel,
+                      int64_t nsel_pad, int ld, const int64_t* __restrict__ top_idx,
+                      const double* __restrict__ top_s64, int k, double factor, double min_gap, double n_rows,
+                      const double* __restrict__ hist_t, const uint32_t* __restrict__ hist_c, double cap_rows,
+                      __nv_bfloat16* __restrict__ qb2, uint32_t* __restrict__ thr_bits, double* __restrict__ tcos,
+                      uint32_t* __restrict__ cnt, int32_t* __restrict__ n_overflow) {
+    const int lane = threadIdx.x & 31;
+    const int64_t i = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (i == 0 && lane == 0) *n_overflow = 0;
+    if (i >= nsel_pad) return;
+    uint4* dst = reinterpret_cast<uint4*>(qb2 + i * ld);
+    if (i >= nsel) {
+        for (int c = lane; c < ld / 8; c += 32) dst[c] = make_uint4(0, 0, 0, 0);
+        if (lane == 0) { thr_bits[i] = __float_as_uint(INFINITY); cnt[i] = 0u; }
+        return;
+    }
+    const int64_t q = qids[i];
+    const uint4* src = reinterpret_cast<const uint4*>(qb + q * ld);
+    double n2 = 0.0;
+    for (int c = lane; c < ld / 8; c += 32) {
+        const uint4 v = src[c];
+        dst[c] = v;
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const double a = (double)__uint_as_float(w[j] << 16), b = (double)__uint_as_float(w[j] & 0xffff0000u);
+            n2 += a * a + b * b;
+        }
+    }
+#pragma unroll
+    for (int j = 16; j > 0; j >>= 1) n2 += shfl_xor_d(n2, j);
+    if (lane == 0) {
+        float t = -INFINITY;
+        double tc = -INFINITY;
+        const double nq = sqrt(n2);
+        const double target = factor * (double)k;
+        if (factor > 0.0 && nq > 0.0 && n_rows >= 256.0 && target < 0.5 * n_rows && top_idx[q * 32 + 31] >= 0) {
+            const double s4 = top_s64[q * 32 + 3], s32 = top_s64[q * 32 + 31];
+            const double z4 = -normcdfinv(4.0 / n_rows), z32 = -normcdfinv(32.0 / n_rows), zt = -normcdfinv(target / n_rows);
+            const double sigma = fmax((s4 - s32) / (z4 - z32), 0.0);
+            double gap = sigma * (z32 - zt);
+            // A previous pass measured how many rows (hc) lie above ITS threshold (ht): a second
+            // point further down the tail, much better than s_4 for the spread (secant step in
+            // z-space).  Whatever the fit says, a threshold that proved too high is followed by a
+            // lower one and a threshold that collected more than the pass can hold by a higher one.
+            const double hc = (double)hist_c[q], ht = hist_t[q];
+            if (hc > 0.0 && ht > -INFINITY) {
+                const double gap_prev = s32 - ht;
+                if (hc > 36.0 && hc < 0.5 * n_rows && gap_prev > 0.0) {
+                    const double zh = -normcdfinv(hc / n_rows);
+                    if (z32 - zh > 1e-6) gap = gap_prev / (z32 - zh) * (z32 - zt);
+                } else if (gap_prev > 0.0) {
+                    gap = 2.0 * gap_prev;
+                }
+                if (hc <= cap_rows) gap = fmax(gap, gap_prev + min_gap);
+                else if (gap_prev - min_gap > 0.0) gap = fmin(gap, gap_prev - min_gap);
+            }
+            gap = fmax(gap, min_gap);
+            t = __double2float_rd((s32 - gap) * nq);
+            if (t == t && fabsf(t) < INFINITY) tc = (double)t / nq;               // what the scan really applies
+            else t = -INFINITY;
+        }
+        thr_bits[i] = __float_as_uint(t);
+        tcos[i] = tc;
+        cnt[i] = 0u;
     }
 }
 
@@ -571,11 +662,26 @@ cudaError_t launch_refine_finish(const uint32_t* cand, const uint32_t* cnt, int 
                                  int ld, const int32_t* qids, int64_t nsel, int64_t capacity, int64_t head,
                                  int64_t base_seq, int64_t seq_mul, int64_t seq_add, int k, int64_t* out_idx,
                                  float* out_score, double* out_score64, uint8_t* overflow, int32_t* n_overflow,
-                                 cudaStream_t st) {
+                                 const double* tcos, double err, double* hist_t, uint32_t* hist_c, cudaStream_t st) {
     if (nsel <= 0) return cudaSuccess;
-    refine_finish_kernel<<<(unsigned)nsel, REFINE_THREADS, (size_t)cap * 16, st>>>(
+    const size_t smem = (size_t)cap * 16;
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(refine_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    refine_finish_kernel<<<(unsigned)nsel, REFINE_THREADS, smem, st>>>(
         cand, cnt, cap, (const __nv_bfloat16*)qb2, (const __nv_bfloat16*)vec, ld, qids, capacity, head, base_seq,
-        seq_mul, seq_add, k, out_idx, out_score, out_score64, overflow, n_overflow);
+        seq_mul, seq_add, k, out_idx, out_score, out_score64, overflow, n_overflow, tcos, err, hist_t, hist_c);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_largek_prepare(const void* qb, const int32_t* qids, int64_t nsel, int64_t nsel_pad, int ld,
+                                  const int64_t* top_idx, const double* top_s64, int k, double factor, double min_gap,
+                                  double n_rows, const double* hist_t, const uint32_t* hist_c, double cap_rows, void* qb2,
+                                  uint32_t* thr_bits, double* tcos, uint32_t* cnt, int32_t* n_overflow, cudaStream_t st) {
+    const unsigned grid = (unsigned)((nsel_pad + 3) / 4);
+    largek_prepare_kernel<<<grid, 128, 0, st>>>((const __nv_bfloat16*)qb, qids, nsel, nsel_pad, ld, top_idx, top_s64, k,
+                                                factor, min_gap, n_rows, hist_t, hist_c, cap_rows, (__nv_bfloat16*)qb2, thr_bits, tcos, cnt, n_overflow);
     return cudaGetLastError();
 }
 

@@ -92,7 +92,11 @@ cudaError_t launch_refine_finish(const uint32_t* cand, const uint32_t* cnt, int 
                                  int ld, const int32_t* qids, int64_t nsel, int64_t capacity, int64_t head,
                                  int64_t base_seq, int64_t seq_mul, int64_t seq_add, int k, int64_t* out_idx,
                                  float* out_score, double* out_score64, uint8_t* overflow, int32_t* n_overflow,
-                                 cudaStream_t st);
+                                 const double* tcos, double err, double* hist_t, uint32_t* hist_c, cudaStream_t st);
+cudaError_t launch_largek_prepare(const void* qb, const int32_t* qids, int64_t nsel, int64_t nsel_pad, int ld,
+                                  const int64_t* top_idx, const double* top_s64, int k, double factor, double min_gap,
+                                  double n_rows, const double* hist_t, const uint32_t* hist_c, double cap_rows, void* qb2,
+                                  uint32_t* thr_bits, double* tcos, uint32_t* cnt, int32_t* n_overflow, cudaStream_t st);
 
 cudaError_t launch_exact(const void* qb, const void* vec, int ld, const int32_t* prio,
                          const uint64_t* tagmask, const int64_t* expires, int64_t nslots,

@@ -213,6 +213,21 @@ class SemanticStore:
                                                   int(min_priority), int(req_tagmask), int(now_us), ptr(idx), ptr(sc),
                                                   ptr(sc64), ptr(inexact), ptr(flags), self._stream()))
 
+    def search_large(self, q, k: int, min_priority: int = 0, req_tagmask: int = 0, now_us: int = 0):
+        """Top-k for 32 < k <= 1024 on the device (pilott_mem_search_large): CUDA fp32 [nq, dim] in,
+        (idx, score, score64) CUDA tensors out; self.last_fallbacks = queries that needed brute force."""
+        torch = _torch()
+        q = q.contiguous()
+        nq = q.shape[0]
+        idx = torch.empty((nq, k), dtype=torch.int64, device=q.device)
+        sc = torch.empty((nq, k), dtype=torch.float32, device=q.device)
+        sc64 = torch.empty((nq, k), dtype=torch.float64, device=q.device)
+        nb = C.c_int32()
+        check(self._lib.pilott_mem_search_large(self._h, ptr(q), nq, int(k), int(min_priority), int(req_tagmask),
+                                                int(now_us), ptr(idx), ptr(sc), ptr(sc64), C.byref(nb), self._stream()))
+        self.last_fallbacks = nb.value
+        return idx, sc, sc64
+
     def search_exact(self, q, k: int, query_ids=None, out=None, min_priority: int = 0, req_tagmask: int = 0,
                      now_us: int = 0):
         """Brute-force fp64 search on the device (any k).  q: CUDA fp32 [nq, dim]."""

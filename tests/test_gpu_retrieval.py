@@ -157,9 +157,15 @@ def test_empty_and_tiny_stores(torch_cuda, kernel):
 def test_exact_path_large_k(torch_cuda):
     gs, os_, x = _fill(4000, 256, 4096, seed=5)
     q = synth.queries(9, 256, seed=6)
-    _check(gs, os_, q, 50)                       # k > 32 -> brute-force fp64 path
+    _check(gs, os_, q, 50)                       # 32 < k <= 1024 -> threshold-collect path (tests/test_gpu_largek.py)
     _check(gs, os_, q, 100, min_priority=1, now_us=1_000_000)
+    assert gs.last_fallbacks == 0                # nobody needed the brute-force kernels
+    _check(gs, os_, q, 1500)                     # k > 1024 -> brute-force fp64 path
     assert gs.last_fallbacks == 9
+    torch = torch_cuda                           # and the brute-force entry point on its own
+    idx, sc, sc64 = gs.search_exact(torch.from_numpy(q).cuda(), 50)
+    oidx, osc = retrieval_c.search(os_, q, 50)
+    assert np.array_equal(idx.cpu().numpy(), oidx) and np.array_equal(sc64.cpu().numpy(), osc)
     gs.close()
 
 
