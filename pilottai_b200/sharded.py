@@ -135,14 +135,19 @@ class ShardedSemanticStore:
         before the exchange; with resolve=False the caller checks the counter search_end() returns."""
         b = self._buffers(q.shape[0], k, q.device, slot)
         xs = self._exchange_for(q.shape[0], k) if self.exchange == "p2p" else None
-        if xs is not None and not resolve:
+        large = k > _lib.MAX_FUSED_K                      # local top-k through the threshold-collect path (exact, synchronous)
+        if xs is not None and not resolve and not large:
             # fused: finish_kernel stores the result rows into every rank's buffer as it produces them
             step = xs[1]
             xs[1] += 1
             self.local.search_publish_into(xs[0], step, q, k, b["idx"], b["sc"], b["sc64"], b["inexact"], b["flags"], **flt)
             return b, ("p2p", xs[0], step, q.shape[0], k)
-        self.local.search_into(q, k, b["idx"], b["sc"], b["sc64"], b["inexact"], b["flags"], **flt)
-        if resolve and int(b["inexact"].item()):
+        if large:
+            self.local.search_large(q, k, out=(b["idx"], b["sc"], b["sc64"]), **flt)
+            b["inexact"].zero_()
+        else:
+            self.local.search_into(q, k, b["idx"], b["sc"], b["sc64"], b["inexact"], b["flags"], **flt)
+        if not large and resolve and int(b["inexact"].item()):
             self.local.refine(q, k, b["flags"].nonzero(), (b["idx"], b["sc"], b["sc64"]), **flt)
             b["inexact"].zero_()
         work = None

@@ -213,15 +213,19 @@ class SemanticStore:
                                                   int(min_priority), int(req_tagmask), int(now_us), ptr(idx), ptr(sc),
                                                   ptr(sc64), ptr(inexact), ptr(flags), self._stream()))
 
-    def search_large(self, q, k: int, min_priority: int = 0, req_tagmask: int = 0, now_us: int = 0):
+    def search_large(self, q, k: int, min_priority: int = 0, req_tagmask: int = 0, now_us: int = 0, out=None):
         """Top-k for 32 < k <= 1024 on the device (pilott_mem_search_large): CUDA fp32 [nq, dim] in,
-        (idx, score, score64) CUDA tensors out; self.last_fallbacks = queries that needed brute force."""
+        (idx, score, score64) CUDA tensors out (or written into `out`); self.last_fallbacks = queries
+        that needed brute force."""
         torch = _torch()
         q = q.contiguous()
         nq = q.shape[0]
-        idx = torch.empty((nq, k), dtype=torch.int64, device=q.device)
-        sc = torch.empty((nq, k), dtype=torch.float32, device=q.device)
-        sc64 = torch.empty((nq, k), dtype=torch.float64, device=q.device)
+        if out is not None:
+            idx, sc, sc64 = out
+        else:
+            idx = torch.empty((nq, k), dtype=torch.int64, device=q.device)
+            sc = torch.empty((nq, k), dtype=torch.float32, device=q.device)
+            sc64 = torch.empty((nq, k), dtype=torch.float64, device=q.device)
         nb = C.c_int32()
         check(self._lib.pilott_mem_search_large(self._h, ptr(q), nq, int(k), int(min_priority), int(req_tagmask),
                                                 int(now_us), ptr(idx), ptr(sc), ptr(sc64), C.byref(nb), self._stream()))

@@ -80,8 +80,12 @@ def _worker(rank, world, port, n, dim, nq, k, out, exchange):
         assert torch.equal(i0, want_i) and torch.equal(s0, want_s)
         assert torch.equal(i1.flip(0), want_i) and torch.equal(s1.flip(0), want_s)
     st.check_exchange()
+    # k > 32: every shard answers through the large-k path, the exchange and the merge are the same
+    i64, _, s64, _ = st.search(q, 64, min_priority=1, now_us=1_000_000)
+    torch.cuda.synchronize()
     if rank == 0:
-        np.save(out + "_i.npy", idx.cpu().numpy()); np.save(out + "_s.npy", sc64.cpu().numpy())
+        np.save(out + "_i.npy", want_i.cpu().numpy()); np.save(out + "_s.npy", want_s.cpu().numpy())
+        np.save(out + "_i64.npy", i64.cpu().numpy()); np.save(out + "_s64.npy", s64.cpu().numpy())
     st.close()
     dist.destroy_process_group()
 
@@ -103,3 +107,6 @@ def test_sharded_search_equals_single_store(torch_cuda, tmp_path, exchange):
     wi, ws = retrieval_c.search(whole, synth.queries(nq, dim, seed=4), k, min_priority=1, now_us=1_000_000)
     assert np.array_equal(np.load(out + "_i.npy"), wi)
     assert np.array_equal(np.load(out + "_s.npy"), ws)
+    wi, ws = retrieval_c.search(whole, synth.queries(nq, dim, seed=4), 64, min_priority=1, now_us=1_000_000)
+    assert np.array_equal(np.load(out + "_i64.npy"), wi)
+    assert np.array_equal(np.load(out + "_s64.npy"), ws)
