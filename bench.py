@@ -232,8 +232,8 @@ def run_ours(args):
     qhost.copy_(qpool.cpu())
     qnp = qhost.numpy()
     h2d, d2h = NQ * DIM * 4, NQ * TOPK * (8 + 4)
-    # Both forms keep two batches in flight: the H2D copy of batch i+1 and the D2H copy of batch i-1
-    # overlap the search of batch i.  Every step's inputs come from pinned host memory and every
+    # Both forms keep several batches in flight (two on one GPU, four in the sharded form): the H2D
+    # copy of batch i+1 and the D2H copy of batch i-1 overlap the search of batch i.  Every step's inputs come from pinned host memory and every
     # step's results are read back to the host inside the timed region.
     if world == 1:
         d2h = NQ * TOPK * (8 + 8 + 4) + NQ + 8          # idx, fp64 + fp32 scores, flags, counter
@@ -245,24 +245,25 @@ def run_ours(args):
                     loc.search_host_end((i - 1) % 2)                    # ... _end: waits, repairs, copies out
             loc.search_host_end((n - 1) % 2)
     else:
+        NSLOT = 4          # batches in flight: the host runs up to three steps ahead of the results it reads
         h2d_s, d2h_s = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
-        qdev = [torch.empty((NQ, DIM), dtype=torch.float32, device=dev) for _ in range(2)]
+        qdev = [torch.empty((NQ, DIM), dtype=torch.float32, device=dev) for _ in range(NSLOT)]
         pack_bytes = NQ * TOPK * 12 + 8                  # merged idx int64 | score fp32 | inexact counter (sharded.py)
-        out_p = [torch.empty(pack_bytes, dtype=torch.uint8).pin_memory() for _ in range(2)]
+        out_p = [torch.empty(pack_bytes, dtype=torch.uint8).pin_memory() for _ in range(NSLOT)]
         out_c = [p[NQ * TOPK * 12: NQ * TOPK * 12 + 4].view(torch.int32) for p in out_p]
-        ev_h2d = [torch.cuda.Event() for _ in range(2)]
-        ev_used = [torch.cuda.Event() for _ in range(2)]
-        ev_done = [torch.cuda.Event() for _ in range(2)]
-        ev_d2h = [torch.cuda.Event() for _ in range(2)]
+        ev_h2d = [torch.cuda.Event() for _ in range(NSLOT)]
+        ev_used = [torch.cuda.Event() for _ in range(NSLOT)]
+        ev_done = [torch.cuda.Event() for _ in range(NSLOT)]
+        ev_d2h = [torch.cuda.Event() for _ in range(NSLOT)]
         d2h = pack_bytes
 
         def e2e_run(n):
             main = torch.cuda.current_stream(dev)
-            tickets = [None, None]
+            tickets = [None] * NSLOT
             flagged = 0
 
             def finish(j):
-                s = j % 2
+                s = j % NSLOT
                 store.search_end(tickets[s])                         # merge into the slot's packed result block
                 ev_done[s].record(main)
                 d2h_s.wait_event(ev_done[s])
@@ -271,9 +272,9 @@ def run_ours(args):
                 ev_d2h[s].record(d2h_s)
 
             for i in range(n):
-                s = i % 2
-                if i >= 2:
-                    ev_d2h[s].synchronize()                          # results of batch i-2 are on the host
+                s = i % NSLOT
+                if i >= NSLOT:
+                    ev_d2h[s].synchronize()                          # results of batch i-NSLOT are on the host
                     flagged += int(out_c[s].item())
                     h2d_s.wait_event(ev_used[s])                     # its queries were consumed
                 with torch.cuda.stream(h2d_s):
@@ -285,7 +286,7 @@ def run_ours(args):
                 if i > 0:
                     finish(i - 1)
             finish(n - 1)
-            for s in range(2):
+            for s in range(min(NSLOT, n)):
                 ev_d2h[s].synchronize()
                 flagged += int(out_c[s].item())
             if flagged:
