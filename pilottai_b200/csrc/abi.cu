@@ -461,6 +461,7 @@ int refine_core(pilott_mem* h, const float* q_dev, int64_t nq, const int32_t* qi
 // LARGEK_CAP collected rows and whatever is left after the last pass go to brute force.
 // Synchronises the stream between passes.
 constexpr int LARGEK_CAP = 4096;
+constexpr int64_t LARGEK_CHUNK = 2048;      // queries per round of passes
 
 int largek_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t min_prio, uint64_t req,
                 int64_t now_us, int64_t* out_idx, float* out_score, double* out_score64, int32_t* n_brute,
@@ -470,6 +471,17 @@ int largek_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
     if (k <= PILOTT_MAX_FUSED_K || k > PILOTT_MAX_LARGE_K || pick_kernel(h) != 3 || h->count == 0) {
         if (n_brute) *n_brute = (int32_t)nq;
         return exact_core(h, q_dev, nq, nullptr, nq, k, min_prio, req, now_us, out_idx, out_score, out_score64, st);
+    }
+    if (nq > LARGEK_CHUNK) {             // 16 KB of candidate slots per query: bound the scratch, batch by batch
+        for (int64_t lo = 0; lo < nq; lo += LARGEK_CHUNK) {
+            const int64_t n = nq - lo < LARGEK_CHUNK ? nq - lo : LARGEK_CHUNK;
+            int32_t nb = 0;
+            const int rcc = largek_core(h, q_dev + lo * h->dim, n, k, min_prio, req, now_us, out_idx + lo * k,
+                                        out_score + lo * k, out_score64 ? out_score64 + lo * k : nullptr, &nb, st);
+            if (rcc) return rcc;
+            if (n_brute) *n_brute += nb;
+        }
+        return PILOTT_OK;
     }
     // 1. fused top-32 into scratch (prepare inside it converts the queries and builds the filter mask)
     const size_t t_idx_b = (size_t)nq * 32 * 8, t_s_b = (size_t)nq * 32 * 4;

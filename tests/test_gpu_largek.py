@@ -90,3 +90,13 @@ def test_large_k_on_a_bursty_corpus(torch_cuda):
     q = (topics[rng.integers(0, topics.shape[0], 40)] + 0.02 * rng.standard_normal((40, dim))).astype(np.float32)
     _same(gs.search(q, k, want_score64=True), os_, q, k)
     gs.close()
+
+
+def test_large_k_many_queries_are_processed_in_rounds(torch_cuda):
+    """More queries than one round of passes takes (2048): results must not depend on the split."""
+    n, dim, nq, k = 20000, 64, 2100, 40
+    x = synth.corpus(n, dim, seed=71)
+    gs, os_ = _pair(x, n)
+    q = synth.queries(nq, dim, seed=72)
+    _same(gs.search(q, k, want_score64=True), os_, q, k)
+    gs.close()
