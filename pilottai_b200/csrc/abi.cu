@@ -454,12 +454,12 @@ int refine_core(pilott_mem* h, const float* q_dev, int64_t nq, const int32_t* qi
 }
 
 // Large k (PILOTT_MAX_FUSED_K < k <= PILOTT_MAX_LARGE_K): fused top-32 first (it supplies s_4 and
-// s_32 of every query), then COLLECT passes whose per-query thresholds are extrapolated guesses at
-// rank 1.5k (refitted from the row count each pass measures) and finally an open threshold; refine_finish_kernel re-scores what a pass
-// collected, ranks it and checks the guess (the k-th exact score must clear every uncollected
-// row); queries whose guess was too high go into the next pass, queries with more than
-// LARGEK_CAP collected rows and whatever is left after the last pass go to brute force.
-// Synchronises the stream between passes.
+// s_32 of every query), then COLLECT passes whose per-query thresholds are guesses at rank 1.5k --
+// from a normal-tail model first, refitted from the row count each pass measures afterwards --
+// and finally an open threshold.  refine_finish_kernel re-scores what a pass collected, ranks it
+// and checks the guess (the k-th exact score must clear every uncollected row); queries that fail
+// the check or collected more than LARGEK_CAP rows go into the next pass, whatever is left after
+// the last one goes to brute force.  Synchronises the stream between passes.
 constexpr int LARGEK_CAP = 4096;
 constexpr int64_t LARGEK_CHUNK = 2048;      // queries per round of passes
 
