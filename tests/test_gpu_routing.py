@@ -100,3 +100,47 @@ def test_router_wide_vocabulary_generic_words(torch_cuda):
         want, ws = ro.router_route(agents, t, 0.8)
         assert (agents[i]["id"] if i >= 0 else None) == want
         assert want is None or float(s).hex() == float(ws).hex()
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_random_tables_match_oracle_in_all_three_modes(torch_cuda, seed):
+    """Seeded fuzz: agent counts that are not multiples of the kernel's unroll, vocabularies of one,
+    two and three+ mask words, agents without the capability attribute or without specializations,
+    tasks with unknown capabilities / types / tags; router, load balancer and delegator modes."""
+    from pilottai_b200.routing import RoutingEngine
+    rng = np.random.default_rng(500 + seed)
+    na = int(rng.choice([1, 2, 3, 5, 17, 63, 130, 257]))
+    extra = int(rng.choice([0, 0, 40, 90, 200]))                 # extra capabilities/specializations -> more words
+    agents = synth.agent_table(na, seed=seed + 60)
+    xc = [f"xc{i}" for i in range(extra)]
+    xs = [f"xs{i}" for i in range(extra)]
+    for a in agents:
+        if a["caps"] is not None:
+            a["caps"] = a["caps"] + [c for c in xc if rng.random() < 0.4]
+        if a["specializations"] is not None:
+            a["specializations"] = a["specializations"] + [s for s in xs if rng.random() < 0.2]
+    tasks = synth.task_table(200, seed=seed + 90)
+    for t in tasks[::2]:
+        if extra and "required_capabilities" in t:
+            t["required_capabilities"] = t["required_capabilities"] + [str(c) for c in rng.choice(xc, 1)]
+        if extra and rng.random() < 0.5:
+            t["type"] = str(rng.choice(xs))
+    eng = RoutingEngine(agents, 0)
+    thr = float(rng.choice([0.5, 0.8, 1.0]))
+    idx, sc = eng.route(tasks, "router", load_threshold=thr)
+    for t, i, s in zip(tasks, idx, sc):
+        want, ws = ro.router_route(agents, t, thr)
+        assert (agents[i]["id"] if i >= 0 else None) == want, (seed, na, extra)
+        assert want is None or float(s).hex() == float(ws).hex()
+    lbm = {a["id"]: ro.lb_metrics(a, 10.0, 20.0) for a in agents}
+    cands = [a["id"] for a in agents]
+    idx, sc = eng.route(tasks, "load_balancer", lb_metrics=lbm, max_tasks_per_agent=60, overload_threshold=thr)
+    for t, i, s in zip(tasks, idx, sc):
+        want, ws = ro.lb_find_best(agents, lbm, t, cands, 60, thr)
+        assert (agents[i]["id"] if i >= 0 else None) == want, (seed, na, extra)
+        assert want is None or float(s).hex() == float(ws).hex()
+    idx, sc = eng.route(tasks, "delegator")
+    for t, i, s in zip(tasks, idx, sc):
+        want, ws = ro.delegator_find_best(agents, t)
+        assert (agents[i]["id"] if i >= 0 else None) == want, (seed, na, extra)
+        assert want is None or float(s).hex() == float(ws).hex()
