@@ -243,9 +243,9 @@ class LoadBalancer:
         loads = [self._calculate_composite_load(m) for m in hist]
         return (loads[-1] - loads[0]) / len(loads)
 
-    async def _analyze_agent_loads(self, current: Dict[str, LoadMetrics]) -> Tuple[List[str], List[str]]:   # :143-159
+    async def _analyze_agent_loads(self, current_metrics: Dict[str, LoadMetrics]) -> Tuple[List[str], List[str]]:   # :143-159
         over, under = [], []
-        for aid, m in current.items():
+        for aid, m in current_metrics.items():
             trend, load = self._calculate_load_trend(aid), self._calculate_composite_load(m)
             if load > self.config.overload_threshold and trend > 0:
                 over.append(aid)
