@@ -371,7 +371,21 @@ class TaskDelegator:
         self.logger = logging.getLogger(f"TaskDelegator_{getattr(agent, 'id', 'agent')}")
         self._delegation_lock = asyncio.Lock()
         self.MAX_HISTORY_PER_AGENT = 1000
+        self.HISTORY_CLEANUP_INTERVAL = 3600
+        self._last_cleanup = datetime.now()
+        self._cleanup_task = None
         self._cache = _EngineCache(device)
+
+    async def start(self):                                          # task_delegator.py:30-31
+        self._cleanup_task = asyncio.create_task(self._periodic_cleanup())
+
+    async def stop(self):                                           # :33-39
+        if self._cleanup_task:
+            self._cleanup_task.cancel()
+            try:
+                await self._cleanup_task
+            except asyncio.CancelledError:
+                pass
 
     async def _should_delegate(self, task: Dict) -> bool:           # task_delegator.py:328-349
         try:
@@ -428,27 +442,74 @@ class TaskDelegator:
             self.logger.error(f"Delegation evaluation failed: {str(e)}")
             return False, None
 
-    def record_delegation(self, agent_id: str, task: Dict, result: Dict):            # :183-219 (condensed)
-        ok = result.get("status") == "completed"
-        hist = self.delegation_history[agent_id]
-        hist.append({"task_id": task["id"], "timestamp": datetime.now().isoformat(), "success": ok,
-                     "execution_time": result.get("execution_time"), "error": result.get("error")})
-        del hist[: max(0, len(hist) - self.MAX_HISTORY_PER_AGENT)]
-        m = self.agent_metrics.setdefault(agent_id, DelegationMetrics())
-        if ok:
-            m.success_count += 1
-            m.last_success = datetime.now()
-        else:
-            m.failure_count += 1
-            m.last_failure = datetime.now()
-            et = str(result.get("error_type", "unknown"))
-            m.error_types[et] = m.error_types.get(et, 0) + 1
-        t = result.get("execution_time") or 0
-        m.total_execution_time += t
-        m.avg_execution_time = m.total_execution_time / max(1, m.success_count + m.failure_count)
-        self.active_delegations.pop(task["id"], None)
+    async def record_delegation(self, agent_id: str, task: Dict, result: Dict):      # :183-219
+        """Book-keeping after a delegated task came back: history entry (capped per agent), the
+        agent's counters and running mean, and the delegation is no longer active."""
+        try:
+            async with self._delegation_lock:
+                ok = result.get("status") == "completed"
+                entry = {"task_id": task["id"], "task": task, "timestamp": datetime.now().isoformat(), "success": ok,
+                         "execution_time": result.get("execution_time", 0), "error": result.get("error"),
+                         "error_type": result.get("error_type")}
+                hist = self.delegation_history[agent_id]
+                hist.append(entry)
+                if len(hist) > self.MAX_HISTORY_PER_AGENT:
+                    hist.pop(0)
+                m = self.agent_metrics.setdefault(agent_id, DelegationMetrics())
+                if ok:
+                    m.success_count += 1
+                    m.last_success = datetime.now()
+                else:
+                    m.failure_count += 1
+                    m.last_failure = datetime.now()
+                    et = entry.get("error_type", "unknown")             # key exists: a missing type is counted under None (:206)
+                    m.error_types[et] = m.error_types.get(et, 0) + 1
+                m.total_execution_time += entry["execution_time"]
+                m.avg_execution_time = m.total_execution_time / (m.success_count + m.failure_count)
+                self.active_delegations.pop(task["id"], None)
+        except Exception as e:
+            self.logger.error(f"Error recording delegation: {str(e)}")
+
+    def get_agent_metrics(self, agent_id: str) -> Optional[Dict[str, Any]]:          # :221-238
+        try:
+            m = self.agent_metrics.get(agent_id)
+            if not m:
+                return None
+            total = m.success_count + m.failure_count
+            return {"success_rate": m.success_count / total if total > 0 else 0,
+                    "avg_execution_time": m.avg_execution_time, "total_tasks": total,
+                    "last_success": m.last_success, "last_failure": m.last_failure,
+                    "error_distribution": m.error_types}
+        except Exception:
+            return None
+
+    async def _periodic_cleanup(self):                                               # :270-278
+        while True:
+            try:
+                await asyncio.sleep(self.HISTORY_CLEANUP_INTERVAL)
+                await self._cleanup_old_history()
+            except asyncio.CancelledError:
+                break
+            except Exception as e:
+                self.logger.error(f"Cleanup error: {str(e)}")
+
+    async def _cleanup_old_history(self):                                            # :280-306
+        """History older than a day goes, delegations that never reported back after an hour too."""
+        try:
+            async with self._delegation_lock:
+                now = datetime.now()
+                day_ago, hour = now - timedelta(hours=24), timedelta(hours=1)
+                for agent_id in list(self.delegation_history.keys()):
+                    kept = [e for e in self.delegation_history[agent_id] if datetime.fromisoformat(e["timestamp"]) > day_ago]
+                    self.delegation_history[agent_id] = kept[-self.MAX_HISTORY_PER_AGENT:]
+                for task_id in [t for t, info in self.active_delegations.items() if now - info["started_at"] > hour]:
+                    self.active_delegations.pop(task_id)
+                self._last_cleanup = now
+        except Exception as e:
+            self.logger.error(f"Error cleaning up history: {str(e)}")
 
     async def get_metrics(self) -> Dict[str, Any]:
         return {"active_delegations": len(self.active_delegations),
                 "agent_metrics": {a: m.model_dump() for a, m in self.agent_metrics.items()},
-                "history_size": sum(len(h) for h in self.delegation_history.values())}
+                "history_size": sum(len(h) for h in self.delegation_history.values()),
+                "last_cleanup": self._last_cleanup.isoformat()}

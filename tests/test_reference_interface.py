@@ -96,4 +96,18 @@ def test_task_delegator_interface(ref):
     from pilottai_b200.orchestration import TaskDelegator
     them = ref["dg"]
     _check_methods(TaskDelegator, them.TaskDelegator,
-                   ["__init__", "evaluate_delegation", "_find_best_agent", "_should_delegate", "get_metrics"])
+                   ["__init__", "start", "stop", "evaluate_delegation", "record_delegation", "get_agent_metrics",
+                    "get_metrics", "_find_best_agent", "_should_delegate", "_periodic_cleanup", "_cleanup_old_history"])
+
+
+def test_every_public_method_of_the_reference_classes_exists_here(ref):
+    from pilottai_b200.knowledge import KnowledgeManager
+    from pilottai_b200.memory import EnhancedMemory
+    from pilottai_b200.orchestration import LoadBalancer, TaskDelegator, TaskRouter
+    pairs = [(EnhancedMemory, ref["mem"].EnhancedMemory), (KnowledgeManager, ref["km"].KnowledgeManager),
+             (TaskRouter, ref["router"].TaskRouter), (LoadBalancer, ref["lb"].LoadBalancer),
+             (TaskDelegator, ref["dg"].TaskDelegator)]
+    for ours, theirs in pairs:
+        public = [n for n, v in inspect.getmembers(theirs, callable) if not n.startswith("_")]
+        missing = [n for n in public if not hasattr(ours, n)]
+        assert not missing, f"{ours.__name__} lacks public methods of the reference: {missing}"

@@ -121,3 +121,21 @@ def test_vocab_and_unknown_capability_flag():
     enc = R.encode_tasks([{"required_capabilities": ["a", "zzz"]}, {"required_capabilities": ["a"]}, {}], v)
     assert list(enc["flags"]) == [1 | 4, 1, 0]                # ... but task flag bit 2
     assert int(v.tag_mask(["x", "x", "nope"])[0]) == 1
+
+
+def test_task_delegator_bookkeeping_matches_the_reference_log(golden_dir):
+    """tests/golden/delegator_session.json is the log of oracle/delegator_script.py run against the
+    UNMODIFIED reference TaskDelegator (oracle/gen_golden_delegator.py): history cap, counters,
+    running mean, error types (a missing type is counted under None, as there), active-delegation
+    removal, day-old history and hour-old delegations dropped by the cleanup, metrics keys."""
+    import asyncio
+    import json
+    import os
+    from oracle.delegator_script import session
+    from pilottai_b200.orchestration import TaskDelegator
+    with open(os.path.join(golden_dir, "delegator_session.json")) as f:
+        want = json.load(f)
+    got = json.loads(json.dumps(asyncio.run(session(TaskDelegator))))
+    assert len(got) == len(want)
+    for g, w in zip(got, want):
+        assert g == w, (g, w)
