@@ -70,150 +70,69 @@ class SemanticMemorySource(KnowledgeSource):
         return [{"text": it.text, "metadata": it.metadata, "tags": sorted(it.tags), "priority": it.priority} for it in items]
 
 
+class _ResultCache(OrderedDict):
+    """Query results by key, youngest at the end: a hit is moved to the young end, an insert evicts
+    from the old end until there is room, every entry dies `ttl` seconds after it was stored."""
+
+    @staticmethod
+    def alive(entry: CacheEntry) -> bool:
+        return (datetime.now() - entry.timestamp).total_seconds() < entry.ttl
+
+    def lookup(self, key: str) -> Optional[Any]:
+        entry = self.get(key)
+        if entry is None:
+            return None
+        if not self.alive(entry):
+            del self[key]
+            return None
+        self.move_to_end(key)
+        entry.access_count += 1
+        entry.last_access = datetime.now()
+        return entry.value
+
+    def insert(self, key: str, value: Any, ttl: int, limit: int) -> None:
+        while len(self) >= limit:
+            self.popitem(last=False)
+        self[key] = CacheEntry(value=value, timestamp=datetime.now(), ttl=ttl)
+        self.move_to_end(key)
+
+    def drop(self, doomed) -> None:
+        for key in [k for k in self if doomed(k, self[k])]:
+            del self[key]
+
+
 class KnowledgeManager:
+    QUERY_TIMEOUT_S = 30            # whole query_knowledge call (:96)
+    CLEANUP_EVERY_S = 3600          # background sweep (:226)
+
     def __init__(self, cache_size: int = 1000, cache_ttl: int = 3600):
-        self.sources: Dict[str, KnowledgeSource] = {}
-        self.cache: "OrderedDict[str, CacheEntry]" = OrderedDict()
-        self.last_updated: Dict[str, datetime] = {}
-        self.source_locks: Dict[str, asyncio.Lock] = {}
-        self.cache_lock = asyncio.Lock()
-        self.MAX_CACHE_SIZE = max(100, cache_size)
+        self.MAX_CACHE_SIZE = max(100, cache_size)               # floors (:36-37)
         self.DEFAULT_CACHE_TTL = max(60, cache_ttl)
+        self.cache = _ResultCache()
+        self.cache_lock = asyncio.Lock()
+        self.sources: Dict[str, KnowledgeSource] = {}
+        self.source_locks: Dict[str, asyncio.Lock] = {}
+        self.last_updated: Dict[str, datetime] = {}
         self.logger = logging.getLogger("KnowledgeManager")
         self._cleanup_task = None
 
+    # ---- lifecycle ------------------------------------------------------------------------------
     async def start(self):
         self._cleanup_task = asyncio.create_task(self._periodic_cleanup())
 
     async def stop(self):
-        if self._cleanup_task:
-            self._cleanup_task.cancel()
+        task = self._cleanup_task
+        if task:
+            task.cancel()
             try:
-                await self._cleanup_task
+                await task
             except asyncio.CancelledError:
                 pass
-
-    async def add_source(self, source: KnowledgeSource) -> bool:            # :62-77
-        try:
-            if source.name in self.sources:
-                raise ValueError(f"Source {source.name} already exists")
-            self.source_locks[source.name] = asyncio.Lock()
-            self.sources[source.name] = source
-            self.last_updated[source.name] = datetime.now()
-            source.is_connected = await self._test_connection(source)
-            return source.is_connected
-        except Exception as e:
-            self.logger.error(f"Error adding source {source.name}: {str(e)}")
-            return False
-
-    async def query_knowledge(self, query: str, source_types: List[str], ttl: Optional[int] = None,
-                              force_refresh: bool = False) -> List[Any]:     # :79-118
-        if not query:
-            raise ValueError("Query cannot be empty")
-        if not source_types:
-            raise ValueError("Source types cannot be empty")
-        key = self._generate_cache_key(query, source_types)
-        results: List[Any] = []
-        try:
-            if not force_refresh:
-                hit = await self._get_from_cache(key)
-                if hit is not None:
-                    return hit
-            async with asyncio.timeout(30):
-                for st in source_types:
-                    src = self.sources.get(st)
-                    if src is None:
-                        continue
-                    try:
-                        async with self.source_locks[st]:
-                            r = await self._query_source_with_retry(src, query)
-                            if r is not None:
-                                results.append(r)
-                    except Exception as e:
-                        self.logger.error(f"Error querying source {st}: {str(e)}")
-                        src.error_count += 1
-                if results:
-                    await self._add_to_cache(key, results, ttl)
-                return results
-        except asyncio.TimeoutError:
-            self.logger.error("Query timed out")
-            return []
-        except Exception as e:
-            self.logger.error(f"Error during knowledge query: {str(e)}")
-            return []
-
-    async def _query_source_with_retry(self, source: KnowledgeSource, query: str) -> Optional[Any]:   # :120-147
-        for attempt in range(source.max_retries):
-            try:
-                if not source.is_connected and not await self._test_connection(source):
-                    raise ConnectionError(f"Source {source.name} is not connected")
-                async with asyncio.timeout(source.timeout):
-                    result = await source.query(query)
-                    source.access_count += 1
-                    source.last_access = datetime.now()
-                    return result
-            except asyncio.TimeoutError:
-                source.error_count += 1
-            except Exception as e:
-                self.logger.error(f"Query failed for source {source.name}, attempt {attempt + 1}: {str(e)}")
-                source.error_count += 1
-                if attempt < source.max_retries - 1:
-                    await asyncio.sleep(source.retry_delay)
-        return None
-
-    async def _test_connection(self, source: KnowledgeSource) -> bool:
-        try:
-            async with asyncio.timeout(source.timeout):
-                ok = bool(await source.connect())
-                source.is_connected = ok or source.is_connected
-                return ok
-        except Exception as e:
-            self.logger.error(f"Connection test failed for {source.name}: {str(e)}")
-            return False
-
-    # ---- LRU + TTL cache (:157-197) -----------------------------------------------------------
-    def _is_cache_entry_valid(self, entry: CacheEntry) -> bool:
-        return (datetime.now() - entry.timestamp).total_seconds() < entry.ttl
-
-    def _generate_cache_key(self, query: str, source_types: List[str]) -> str:
-        return json.dumps({"query": query, "sources": sorted(source_types)}, sort_keys=True)
-
-    async def _get_from_cache(self, key: str) -> Optional[Any]:
-        async with self.cache_lock:
-            entry = self.cache.get(key)
-            if entry is None:
-                return None
-            if not self._is_cache_entry_valid(entry):
-                del self.cache[key]
-                return None
-            self.cache.move_to_end(key)
-            entry.access_count += 1
-            entry.last_access = datetime.now()
-            return entry.value
-
-    async def _add_to_cache(self, key: str, value: Any, ttl: Optional[int] = None):
-        async with self.cache_lock:
-            while len(self.cache) >= self.MAX_CACHE_SIZE:
-                self.cache.popitem(last=False)
-            self.cache[key] = CacheEntry(value=value, timestamp=datetime.now(), ttl=ttl or self.DEFAULT_CACHE_TTL)
-            self.cache.move_to_end(key)
-
-    async def invalidate_cache(self, source_name: Optional[str] = None, pattern: Optional[str] = None):
-        async with self.cache_lock:
-            if source_name:
-                doomed = [k for k in self.cache if source_name in json.loads(k)["sources"]]
-            elif pattern:
-                doomed = [k for k in self.cache if pattern in k]
-            else:
-                self.cache.clear()
-                return
-            for k in doomed:
-                del self.cache[k]
 
     async def _periodic_cleanup(self):
         while True:
             try:
-                await asyncio.sleep(3600)
+                await asyncio.sleep(self.CLEANUP_EVERY_S)
                 await self.cleanup()
             except asyncio.CancelledError:
                 break
@@ -221,21 +140,136 @@ class KnowledgeManager:
                 self.logger.error(f"Periodic cleanup error: {str(e)}")
 
     async def cleanup(self):                                     # :226-249
+        """Expired results go; a source that failed more often than it may retry is re-tested and,
+        if it answers, starts over with a clean error count."""
         async with self.cache_lock:
-            for k in [k for k, v in self.cache.items() if not self._is_cache_entry_valid(v)]:
-                del self.cache[k]
-            for source in self.sources.values():
-                if source.error_count > source.max_retries:
-                    source.is_connected = False
-                    if await self._test_connection(source):
-                        source.error_count = 0
-                        source.is_connected = True
+            self.cache.drop(lambda _k, entry: not self._is_cache_entry_valid(entry))
+            for src in self.sources.values():
+                if src.error_count <= src.max_retries:
+                    continue
+                src.is_connected = False
+                if await self._test_connection(src):
+                    src.error_count, src.is_connected = 0, True
 
+    # ---- sources (:62-77, :120-155) ---------------------------------------------------------------
+    async def add_source(self, source: KnowledgeSource) -> bool:
+        name = source.name
+        try:
+            if name in self.sources:
+                raise ValueError(f"Source {name} already exists")
+            self.sources[name], self.source_locks[name] = source, asyncio.Lock()
+            self.last_updated[name] = datetime.now()
+            source.is_connected = await self._test_connection(source)
+            return source.is_connected
+        except Exception as e:
+            self.logger.error(f"Error adding source {name}: {str(e)}")
+            return False
+
+    async def _test_connection(self, source: KnowledgeSource) -> bool:
+        try:
+            async with asyncio.timeout(source.timeout):
+                return await source.connect()             # the flag itself is set by add_source / cleanup only
+        except Exception as e:
+            self.logger.error(f"Connection test failed for {source.name}: {str(e)}")
+            return False
+
+    async def _query_source_with_retry(self, source: KnowledgeSource, query: str) -> Optional[Any]:
+        """Up to max_retries attempts; every failed one counts as an error, a pause of retry_delay
+        separates attempts that failed with anything but a timeout."""
+        last = source.max_retries - 1
+        for attempt in range(source.max_retries):
+            pause = False
+            try:
+                if not (source.is_connected or await self._test_connection(source)):
+                    raise ConnectionError(f"Source {source.name} is not connected")
+                async with asyncio.timeout(source.timeout):
+                    answer = await source.query(query)
+                    source.access_count += 1
+                    source.last_access = datetime.now()
+                    return answer
+            except asyncio.TimeoutError:
+                source.error_count += 1
+            except Exception as e:
+                self.logger.error(f"Query failed for source {source.name}, attempt {attempt + 1}: {str(e)}")
+                source.error_count += 1
+                pause = attempt < last
+            if pause:
+                await asyncio.sleep(source.retry_delay)
+        return None
+
+    # ---- the query (:79-118) ----------------------------------------------------------------------
+    async def query_knowledge(self, query: str, source_types: List[str], ttl: Optional[int] = None,
+                              force_refresh: bool = False) -> List[Any]:
+        if not query:
+            raise ValueError("Query cannot be empty")
+        if not source_types:
+            raise ValueError("Source types cannot be empty")
+        key = self._generate_cache_key(query, source_types)
+        try:
+            if not force_refresh:
+                cached = await self._get_from_cache(key)
+                if cached is not None:
+                    return cached
+            async with asyncio.timeout(self.QUERY_TIMEOUT_S):
+                answers = []
+                for name in source_types:                        # unknown names are skipped
+                    if name in self.sources:
+                        answer = await self._ask(name, query)
+                        if answer is not None:
+                            answers.append(answer)
+                if answers:
+                    await self._add_to_cache(key, answers, ttl)
+                return answers
+        except asyncio.TimeoutError:
+            self.logger.error("Query timed out")
+        except Exception as e:
+            self.logger.error(f"Error during knowledge query: {str(e)}")
+        return []
+
+    async def _ask(self, name: str, query: str) -> Optional[Any]:
+        source = self.sources[name]
+        try:
+            async with self.source_locks[name]:
+                return await self._query_source_with_retry(source, query)
+        except Exception as e:
+            self.logger.error(f"Error querying source {name}: {str(e)}")
+            source.error_count += 1
+            return None
+
+    # ---- result cache (:157-221) --------------------------------------------------------------------
+    def _generate_cache_key(self, query: str, source_types: List[str]) -> str:
+        return json.dumps({"query": query, "sources": sorted(source_types)}, sort_keys=True)
+
+    def _is_cache_entry_valid(self, entry: CacheEntry) -> bool:
+        return _ResultCache.alive(entry)
+
+    async def _get_from_cache(self, key: str) -> Optional[Any]:
+        async with self.cache_lock:
+            return self.cache.lookup(key)
+
+    async def _add_to_cache(self, key: str, value: Any, ttl: Optional[int] = None):
+        async with self.cache_lock:
+            self.cache.insert(key, value, ttl or self.DEFAULT_CACHE_TTL, self.MAX_CACHE_SIZE)
+
+    async def invalidate_cache(self, source_name: Optional[str] = None, pattern: Optional[str] = None):
+        """By source (every result that source contributed to), else by substring of the key, else all."""
+        async with self.cache_lock:
+            if source_name:
+                self.cache.drop(lambda key, _e: source_name in json.loads(key)["sources"])
+            elif pattern:
+                self.cache.drop(lambda key, _e: pattern in key)
+            else:
+                self.cache.clear()
+
+    # ---- introspection ------------------------------------------------------------------------------
     def get_source_stats(self) -> Dict[str, Dict[str, Any]]:
-        return {n: {"access_count": s.access_count, "error_count": s.error_count,
-                    "last_access": s.last_access.isoformat(), "is_connected": s.is_connected}
-                for n, s in self.sources.items()}
+        stats = {}
+        for name, src in self.sources.items():
+            stats[name] = {"access_count": src.access_count, "error_count": src.error_count,
+                           "last_access": src.last_access.isoformat(), "is_connected": src.is_connected}
+        return stats
 
     def get_cache_stats(self) -> Dict[str, Any]:
-        return {"size": len(self.cache), "max_size": self.MAX_CACHE_SIZE,
-                "hit_ratio": sum(e.access_count for e in self.cache.values()) / max(1, len(self.cache))}
+        n = len(self.cache)
+        return {"size": n, "max_size": self.MAX_CACHE_SIZE,
+                "hit_ratio": sum(e.access_count for e in self.cache.values()) / max(1, n)}
