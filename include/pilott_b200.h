@@ -63,7 +63,8 @@ int pilott_mem_info(const pilott_mem_t* h, int64_t* total, int64_t* count, int64
  * which = 5 / 6: reported index = sequence * stride (5) + offset (6); a row-sharded store that
  *            holds global rows i with i % world == rank uses stride = world, offset = rank.
  * which = 7: set `total` (rows ever appended, >= rows held): a restored snapshot continues the
- *            sequence numbering of the store it was taken from. */
+ *            sequence numbering of the store it was taken from.
+ * which = 8: survivors finish_kernel re-scores exactly per query: 0 auto (32), 16 (applies when k <= 12), 32. */
 int pilott_mem_set_option(pilott_mem_t* h, int which, int64_t value);
 /* Kernel launches enqueued by this handle since creation (bench bookkeeping). */
 int64_t pilott_mem_launch_count(const pilott_mem_t* h);

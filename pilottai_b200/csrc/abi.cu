@@ -153,6 +153,7 @@ struct pilott_mem {
     int opt_ctas = 0;
     int opt_dbg = 0;
     int opt_list_len = 0;   // 0 auto, 8, 16, 32
+    int opt_pool = 0;       // 0 auto (32), 16, 32: survivors finish_kernel re-scores
     int auto_min_list = 8;  // floor of the automatic list length: raised when searches keep flagging queries
     int64_t searches_since_refine = 0;
     int64_t seq_mul = 1, seq_add = 0;   // reported index = seq * seq_mul + seq_add (row-sharded stores)
@@ -314,7 +315,8 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
         if (e1) CK(cudaEventRecord(e1, st));
     }
     f.partials = a.partials; f.slots = lists; f.list_len = a.list_len; f.qb = h->qbuf.p; f.vec = h->vec; f.ld = h->ld;
-    f.pool_n = 32;   // always re-score 32 survivors: a wide margin below the k-th keeps the gap check quiet at 10M+ rows
+    // survivors re-scored exactly: 32 (a wide margin below the k-th keeps the gap check quiet), or what option 8 says
+    f.pool_n = (h->opt_pool == 16 && k <= 12) ? 16 : 32;
     f.nq = nq; f.capacity = h->capacity; f.head = h->head; f.base_seq = h->total - h->count;
     f.k = k; f.seq_mul = h->seq_mul; f.seq_add = h->seq_add;
     f.err = h->ld * 2.4e-7 > 1e-4 ? h->ld * 2.4e-7 : 1e-4;
@@ -680,6 +682,9 @@ int pilott_mem_set_option(pilott_mem_t* h, int which, int64_t value) {
     } else if (which == 3) {
         if (value != 0 && value != 8 && value != 16 && value != 32) return fail(PILOTT_EINVAL, "list length must be 0, 8, 16 or 32");
         h->opt_list_len = (int)value;
+    } else if (which == 8) {
+        if (value != 0 && value != 16 && value != 32) return fail(PILOTT_EINVAL, "survivor count must be 0, 16 or 32");
+        h->opt_pool = (int)value;
     } else if (which == 2) {
         h->opt_dbg = (int)value;      // developer switches (profiling experiments); 0 = off
     } else {
