@@ -22,7 +22,7 @@ An agent row is a plain dict (same format as the test oracle uses):
 from __future__ import annotations
 
 import ctypes as C
-from typing import Dict, Iterable, List, Optional, Sequence, Tuple
+from typing import Dict, Iterable, List, Sequence, Tuple
 
 import numpy as np
 

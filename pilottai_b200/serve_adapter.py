@@ -17,7 +17,7 @@ Works with any object that has the same attributes (`agents`, `_select_agent`,
 from __future__ import annotations
 
 import types
-from typing import Any, Dict, Optional
+from typing import Any, Dict
 
 
 def task_to_dict(task: Any) -> Dict[str, Any]:

@@ -5,7 +5,7 @@ worst case for per-list candidate lists.  Prints fallback counts and time per ba
 candidate-list length.   usage: python tools/bench_clustered.py [n] [dim] [nq] [burst] [k] [list length of the device-path timing]"""
 import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import numpy as np, torch
+import torch
 from pilottai_b200.store import SemanticStore
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000

@@ -2,8 +2,7 @@
 usage: python tools/quick_bench.py [n] [dim] [nq] [iters] [kernels,comma]"""
 import sys, os, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import numpy as np, torch
-from pilottai_b200 import synth
+import torch
 from pilottai_b200.store import SemanticStore
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000

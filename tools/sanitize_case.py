@@ -2,7 +2,6 @@
 fallback, routing.  usage: compute-sanitizer --tool memcheck python tools/sanitize_case.py"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import numpy as np
 from pilottai_b200 import synth
 from pilottai_b200.store import SemanticStore
 from pilottai_b200.routing import RoutingEngine
