@@ -64,7 +64,8 @@ int pilott_mem_info(const pilott_mem_t* h, int64_t* total, int64_t* count, int64
  *            holds global rows i with i % world == rank uses stride = world, offset = rank.
  * which = 7: set `total` (rows ever appended, >= rows held): a restored snapshot continues the
  *            sequence numbering of the store it was taken from.
- * which = 8: survivors finish_kernel re-scores exactly per query: 0 auto (32), 16 (applies when k <= 12), 32. */
+ * which = 8: survivors finish_kernel re-scores exactly per query: 0 auto (32), 16 (applies when k <= 12), 32.
+ * which = 9: form of the finish step: 0 one kernel, 1 split into a merge kernel and a re-score kernel. */
 int pilott_mem_set_option(pilott_mem_t* h, int which, int64_t value);
 /* Kernel launches enqueued by this handle since creation (bench bookkeeping). */
 int64_t pilott_mem_launch_count(const pilott_mem_t* h);

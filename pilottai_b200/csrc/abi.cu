@@ -142,7 +142,7 @@ struct pilott_mem {
     int64_t* expires = nullptr;
     float* scale = nullptr;
     float* tile_max = nullptr;
-    DevBuf qbuf, partials, gthr, exact_scratch, stage_dev, result_dev, misc_dev, refine, result_ids, largek;
+    DevBuf qbuf, partials, gthr, exact_scratch, stage_dev, result_dev, misc_dev, refine, result_ids, largek, surv;
     HostBuf stage_host;
     cudaStream_t own_stream = nullptr;
     cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;   // copy streams of the pipelined host path
@@ -154,6 +154,7 @@ struct pilott_mem {
     int opt_dbg = 0;
     int opt_list_len = 0;   // 0 auto, 8, 16, 32
     int opt_pool = 0;       // 0 auto (32), 16, 32: survivors finish_kernel re-scores
+    int opt_finish = 0;     // 0 one kernel, 1 split (merge kernel + re-score kernel)
     int auto_min_list = 8;  // floor of the automatic list length: raised when searches keep flagging queries
     int64_t searches_since_refine = 0;
     int64_t seq_mul = 1, seq_add = 0;   // reported index = seq * seq_mul + seq_add (row-sharded stores)
@@ -326,8 +327,13 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
         f.peers = x->peers_dev; f.world = x->world; f.rank = x->rank; f.block_bytes = x->block_bytes;
         f.flags_off = x->flags_off; f.step = step; f.done_counter = x->done_dev;
     }
+    if (h->opt_finish == 1) {
+        rc = h->surv.ensure((size_t)nq * 33 * 8);
+        if (rc) return rc;
+        f.surv = (uint64_t*)h->surv.p;
+    }
     CK(pilott::launch_finish(f, st));
-    h->launches += 2;
+    h->launches += f.surv ? 3 : 2;
     return PILOTT_OK;
 }
 
@@ -615,6 +621,7 @@ int pilott_mem_create(int dim, int64_t capacity, int device, pilott_mem_t** out)
     }
     if (rc != PILOTT_OK) { free_columns(h); delete h; return rc; }
     CK(cudaDeviceSynchronize());
+    if (const char* f = getenv("PILOTT_FINISH_FORM")) h->opt_finish = atoi(f) == 1 ? 1 : 0;   // developer switch (option 9)
     *out = h;
     return PILOTT_OK;
 }
@@ -625,7 +632,7 @@ int pilott_mem_destroy(pilott_mem_t* h) {
     cudaDeviceSynchronize();
     free_columns(h);
     h->qbuf.release(); h->partials.release(); h->gthr.release(); h->exact_scratch.release(); h->stage_dev.release();
-    h->result_dev.release(); h->misc_dev.release(); h->refine.release(); h->result_ids.release(); h->largek.release();
+    h->result_dev.release(); h->misc_dev.release(); h->refine.release(); h->result_ids.release(); h->largek.release(); h->surv.release();
     h->stage_host.release();
     for (cudaEvent_t e : h->ev) cudaEventDestroy(e);
     for (auto& sl : h->hslot) {
@@ -682,6 +689,9 @@ int pilott_mem_set_option(pilott_mem_t* h, int which, int64_t value) {
     } else if (which == 3) {
         if (value != 0 && value != 8 && value != 16 && value != 32) return fail(PILOTT_EINVAL, "list length must be 0, 8, 16 or 32");
         h->opt_list_len = (int)value;
+    } else if (which == 9) {
+        if (value != 0 && value != 1) return fail(PILOTT_EINVAL, "finish form must be 0 or 1");
+        h->opt_finish = (int)value;
     } else if (which == 8) {
         if (value != 0 && value != 16 && value != 32) return fail(PILOTT_EINVAL, "survivor count must be 0, 16 or 32");
         h->opt_pool = (int)value;

@@ -335,8 +335,204 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_l
     }
 }
 
+// ---------------------------------------------------------------------------------------
+// The same finish in two kernels (FinishArgs::split).  finish_kernel is bound by dependent
+// latencies at 4 CTAs of 124 registers per SM; split, the merge runs one WARP per query (every
+// query of a 1024-batch resident at once) and the re-score stages 16 rows at a time and gives
+// each lane ONE partial sum, so 7 CTAs fit an SM and the batch takes one wave.
+// ---------------------------------------------------------------------------------------
+constexpr int SURV_WORDS = 33;            // per query: 32 survivor keys (descending) + the bound
+
+__global__ void __launch_bounds__(128)
+merge_lists_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_len, int pool_n, int rows_per_group,
+                   int lists_base, int groups_rem, int lists_extra, int64_t nq, const uint32_t* __restrict__ gthr,
+                   uint64_t* __restrict__ surv) {
+    const int lane = threadIdx.x & 31;
+    const int64_t q = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (q >= nq) return;
+    const int per_load = 32 / list_len;
+    const int slots = lists_base + ((q / rows_per_group) < groups_rem ? lists_extra : 0);
+    const uint64_t* p = partials + q * (int64_t)slots_alloc * list_len;
+    const int nloads = (slots + per_load - 1) / per_load;
+    uint64_t best = 0ull, bound = 0ull, drop = 0ull;
+    for (int i0 = 0; i0 < nloads; i0 += 4) {
+        uint64_t x[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {                      // four loads in flight before any sort
+            const int li = (i0 + u) * per_load + lane / list_len;
+            x[u] = (i0 + u < nloads && li < slots) ? __ldcg(p + (int64_t)li * list_len + (lane % list_len)) : 0ull;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (i0 + u >= nloads) break;
+            uint64_t mn = x[u];                            // per-list minimum: a FULL list may have dropped rows <= it
+            for (int j = list_len / 2; j > 0; j >>= 1) {
+                const uint64_t o = shfl_xor64(mn, j);
+                mn = mn < o ? mn : o;
+            }
+            if (mn != 0ull && mn > bound) bound = mn;
+            const uint64_t xs = warp_sort64<false>(x[u], lane);
+            const uint64_t lo = best < xs ? best : xs;     // the 32 keys this merge drops
+            drop = drop > lo ? drop : lo;
+            best = warp_bitonic_merge_desc(best > xs ? best : xs, lane);
+        }
+    }
+    if (pool_n < 32) {
+        const uint64_t cut = shfl64(best, pool_n);
+        drop = drop > cut ? drop : cut;
+        if (lane >= pool_n) best = 0ull;
+    }
+    bound = bound > drop ? bound : drop;
+#pragma unroll
+    for (int j = 16; j > 0; j >>= 1) {
+        const uint64_t o = shfl_xor64(bound, j);
+        bound = bound > o ? bound : o;
+    }
+    if (gthr) {                                            // rows dropped by a threshold scored below it
+        const uint32_t g = __ldcg(gthr + q);
+        const uint64_t gk = ((uint64_t)g << 32) | 0xFFFFFFFFull;
+        if (g != 0u && gk > bound) bound = gk;
+    }
+    surv[q * SURV_WORDS + lane] = best;
+    if (lane == 0) surv[q * SURV_WORDS + 32] = bound;
+}
+
+constexpr int RS_ROWS = 16;               // survivor rows staged per round
+
+__global__ void __launch_bounds__(FIN_WARPS * 32, 7)
+rescore_kernel(const uint64_t* __restrict__ surv, const __nv_bfloat16* __restrict__ qb,
+               const __nv_bfloat16* __restrict__ vec, int ld, int64_t nq, int64_t capacity, int64_t head,
+               int64_t base_seq, int64_t seq_mul, int64_t seq_add, int k, double err, int64_t* __restrict__ out_idx,
+               float* __restrict__ out_score, double* __restrict__ out_score64, uint8_t* __restrict__ flags,
+               int32_t* __restrict__ inexact, unsigned char* const* __restrict__ peers, int world, int rank,
+               int64_t block_bytes, int64_t flags_off, int64_t step, uint32_t* __restrict__ done_counter) {
+    extern __shared__ __align__(16) unsigned char s_rows[];     // [RS_ROWS + 1][ld*2 + 16]: rows of the round, then the query
+    __shared__ double s_part[3][FIN_WARPS][32];                  // pair sums p[2w] + p[2w+1] of (dot, nq, nm) per candidate
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t q = blockIdx.x;
+    const uint64_t key = __ldcg(surv + q * SURV_WORDS + lane);  // lane = candidate (every warp holds all 32)
+    const uint64_t bound = __ldcg(surv + q * SURV_WORDS + 32);
+    const size_t row_bytes = (size_t)ld * 2 + 16;
+    const int chunks = ld / 8;
+    const unsigned char* qrow_s = s_rows + RS_ROWS * row_bytes;
+    const int c = lane & 15, half = lane >> 4;                   // candidate within the round, which partial of the pair
+    for (int round = 0; round < 32 / RS_ROWS; ++round) {
+        if (round) __syncthreads();                              // the previous round's rows are no longer read
+        for (int r = warp; r < RS_ROWS + (round == 0 ? 1 : 0); r += FIN_WARPS) {
+            const __nv_bfloat16* src;
+            if (r == RS_ROWS) src = qb + q * ld;
+            else {
+                const uint64_t kr = __shfl_sync(0xffffffffu, key, round * RS_ROWS + r);
+                if (kr == 0ull) continue;
+                int64_t slot = head + key_age(kr);
+                if (slot >= capacity) slot -= capacity;
+                src = vec + slot * ld;
+            }
+            for (int x = lane; x < chunks; x += 32) cp_async16(s_rows + r * row_bytes + 16 * x, src + 8 * x);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncthreads();
+        // lane (c, half) accumulates partial sum j = 2*warp + half of the stated rule for candidate
+        // round*16 + c: elements d = j, j+8, ... in ascending order
+        const uint64_t kc = __shfl_sync(0xffffffffu, key, round * RS_ROWS + c);
+        double pd = 0.0, pq = 0.0, pm = 0.0;
+        if (kc != 0ull) {
+            const unsigned char* mrow_s = s_rows + c * row_bytes;
+            const int j = 2 * warp + half;
+            for (int d = j; d < ld; d += 8) {
+                const double qv = (double)__uint_as_float((uint32_t)(*reinterpret_cast<const uint16_t*>(qrow_s + 2 * d)) << 16);
+                const double mv = (double)__uint_as_float((uint32_t)(*reinterpret_cast<const uint16_t*>(mrow_s + 2 * d)) << 16);
+                pd = __fma_rn(qv, mv, pd); pq = __fma_rn(qv, qv, pq); pm = __fma_rn(mv, mv, pm);
+            }
+        }
+        // p[2w] + p[2w+1]: one rounding, the same sum whichever lane forms it
+        const double sd = __dadd_rn(pd, shfl_xor_d(pd, 16)), sq = __dadd_rn(pq, shfl_xor_d(pq, 16)), sm = __dadd_rn(pm, shfl_xor_d(pm, 16));
+        if (half == 0) {
+            s_part[0][warp][round * RS_ROWS + c] = sd;
+            s_part[1][warp][round * RS_ROWS + c] = sq;
+            s_part[2][warp][round * RS_ROWS + c] = sm;
+        }
+    }
+    __syncthreads();
+    if (warp != 0) return;
+    const bool pool_full = bound != 0ull;
+    const bool valid = key != 0ull;
+    double sc = -INFINITY, nqn = 0.0;
+    int64_t seq = INT64_MAX;
+    if (valid) {
+        const double dt = __dadd_rn(__dadd_rn(s_part[0][0][lane], s_part[0][1][lane]), __dadd_rn(s_part[0][2][lane], s_part[0][3][lane]));
+        nqn = __dadd_rn(__dadd_rn(s_part[1][0][lane], s_part[1][1][lane]), __dadd_rn(s_part[1][2][lane], s_part[1][3][lane]));
+        const double nmt = __dadd_rn(__dadd_rn(s_part[2][0][lane], s_part[2][1][lane]), __dadd_rn(s_part[2][2][lane], s_part[2][3][lane]));
+        const double den = __dmul_rn(__dsqrt_rn(nqn), __dsqrt_rn(nmt));
+        sc = den > 0.0 ? __ddiv_rn(dt, den) : 0.0;
+        seq = base_seq + key_age(key);
+    }
+    nqn = __longlong_as_double((long long)shfl64((uint64_t)__double_as_longlong(nqn), 0));   // lane 0 is valid whenever pool_full
+    warp_sort_pairs(sc, seq, lane);
+    if (lane < k) {
+        const bool ok = seq != INT64_MAX;
+        out_idx[q * k + lane] = ok ? seq * seq_mul + seq_add : -1;
+        out_score[q * k + lane] = ok ? (float)sc : -INFINITY;
+        if (out_score64) out_score64[q * k + lane] = ok ? sc : -INFINITY;
+    }
+    if (peers) {                                           // row-sharded store: see finish_kernel step 4b
+        const int slot = (int)(step & 3);
+        if (lane < k) {
+            const bool ok = seq != INT64_MAX;
+            const int64_t iw = ok ? seq * seq_mul + seq_add : -1;
+            const int64_t sw = __double_as_longlong(ok ? sc : -INFINITY);
+            for (int p = 0; p < world; ++p) {
+                int64_t* blk = reinterpret_cast<int64_t*>(peers[p] + ((int64_t)slot * world + rank) * block_bytes);
+                blk[q * k + lane] = iw;
+                blk[nq * k + q * k + lane] = sw;
+            }
+        }
+        __syncwarp();
+        if (lane == 0) {
+            __threadfence_system();
+            const uint32_t old = atomicAdd(done_counter, 1u);
+            if (old == (uint32_t)(nq - 1)) {
+                *done_counter = 0u;
+                __threadfence_system();
+                for (int p = 0; p < world; ++p) {
+                    uint64_t* flag = reinterpret_cast<uint64_t*>(peers[p] + flags_off) + (int64_t)slot * world + rank;
+                    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(flag), "l"((uint64_t)(step + 1)) : "memory");
+                }
+            }
+        }
+    }
+    const double e_k = __longlong_as_double((long long)shfl64((uint64_t)__double_as_longlong(sc), k - 1));
+    if (lane == 0) {
+        bool bad = false;
+        if (pool_full) {
+            const double a_min = nqn > 0.0 ? (double)key_score(bound) / sqrt(nqn) : 0.0;
+            bad = !(a_min + err < e_k);
+        }
+        if (flags) flags[q] = bad ? 1 : 0;
+        if (bad && inexact) atomicAdd(inexact, 1);
+    }
+}
+
 cudaError_t launch_finish(const FinishArgs& a, cudaStream_t st) {
     if (a.nq <= 0) return cudaSuccess;
+    const size_t row_bytes = (size_t)a.ld * 2 + 16;
+    if (a.surv && (RS_ROWS + 1) * row_bytes <= 100 * 1024) {
+        // split form: merge (warp per query) + re-score (CTA per query, 16 rows staged per round)
+        merge_lists_kernel<<<(unsigned)((a.nq + 3) / 4), 128, 0, st>>>(
+            a.partials, a.slots, a.list_len, a.pool_n, a.rows_per_group, a.lists_base, a.groups_rem, a.lists_extra, a.nq,
+            a.gthr, a.surv);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+        const size_t smem2 = (RS_ROWS + 1) * row_bytes;
+        e = cudaFuncSetAttribute(rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
+        if (e != cudaSuccess) return e;
+        rescore_kernel<<<(unsigned)a.nq, FIN_WARPS * 32, smem2, st>>>(
+            a.surv, (const __nv_bfloat16*)a.qb, (const __nv_bfloat16*)a.vec, a.ld, a.nq, a.capacity, a.head, a.base_seq,
+            a.seq_mul, a.seq_add, a.k, a.err, a.out_idx, a.out_score, a.out_score64, a.flags, a.inexact, a.peers, a.world,
+            a.rank, a.block_bytes, a.flags_off, a.step, a.done_counter);
+        return cudaGetLastError();
+    }
     // stage the surviving rows in shared memory when they fit (pool_n + 1 rows of ld*2+16 bytes)
     const size_t smem = (size_t)(a.pool_n + 1) * ((size_t)a.ld * 2 + 16);
     const int stage_rows = smem <= 100 * 1024 ? 1 : 0;

@@ -73,6 +73,7 @@ struct FinishArgs {
     int world = 1, rank = 0;
     int64_t block_bytes = 0, flags_off = 0, step = 0;
     uint32_t* done_counter = nullptr;
+    uint64_t* surv = nullptr;   // [nq][33] scratch: set = use the split form (merge kernel + re-score kernel)
 };
 cudaError_t launch_finish(const FinishArgs& a, cudaStream_t st);
 

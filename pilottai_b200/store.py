@@ -68,6 +68,9 @@ class SemanticStore:
     def set_list_len(self, n: int) -> None:
         check(self._lib.pilott_mem_set_option(self._h, 3, int(n)))
 
+    def set_finish_form(self, split: int) -> None:
+        check(self._lib.pilott_mem_set_option(self._h, 9, int(split)))
+
     def set_pool(self, n: int) -> None:
         check(self._lib.pilott_mem_set_option(self._h, 8, int(n)))
 

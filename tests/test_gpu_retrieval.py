@@ -272,3 +272,16 @@ def test_wide_vectors_unstaged_rescore(torch_cuda, kernel):
     _check(gs, os_, q, 10)
     _check(gs, os_, q, 24, min_priority=1)
     gs.close()
+
+
+def test_split_finish_form_gives_the_same_answers(torch_cuda):
+    """Option 9: the finish step as two kernels (merge per warp, re-score with 16 rows staged per
+    round and one partial sum per lane) -- same indices, same fp64 scores, same flags."""
+    gs, os_, x = _fill(9000, 768, 8192, seed=21)          # ring wrapped once
+    q = synth.queries(300, 768, seed=22)
+    for form in (1, 0, 1):
+        gs.set_finish_form(form)
+        _check(gs, os_, q, 10)
+        _check(gs, os_, q, 32, min_priority=1, now_us=1_000_000)
+        _check(gs, os_, q[:3], 1, req_tagmask=0b11)
+    gs.close()

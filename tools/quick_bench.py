@@ -16,6 +16,7 @@ dev = torch.device("cuda:0")
 g = torch.Generator(device=dev); g.manual_seed(1234)
 st = SemanticStore(dim, n, 0)
 st.set_pool(int(os.environ.get("QB_POOL", "0")))
+st.set_finish_form(int(os.environ.get("QB_SPLIT", "0")))
 t0 = time.time()
 for lo in range(0, n, 131072):
     m = min(131072, n - lo)
