@@ -10,6 +10,14 @@
  * pilott/memory/enhanced_memory.py:85,103; pilott/core/router.py:37); different
  * handles are independent.
  *
+ * Streams: entry points that take device pointers enqueue on the CALLER's `stream`; the
+ * *_host entry points enqueue on a stream the handle owns.  The library orders the two
+ * itself (an event behind every call, waited for by the next call of the other family), so a
+ * device append followed by a host search sees the new rows, and a host search still in
+ * flight (pilott_mem_search_host_begin) is not disturbed by a device search that follows.
+ * Two device-pointer calls on DIFFERENT caller streams are the caller's to order: they
+ * share the handle's scratch buffers.
+ *
  * Citations are paths under the reference tree (appyjain21/pilottai).
  */
 #ifndef PILOTT_B200_H
@@ -57,15 +65,17 @@ int pilott_mem_info(const pilott_mem_t* h, int64_t* total, int64_t* count, int64
                     int* dim, int* row_stride);
 /* which = 0: scan kernel (0 auto, 1 generic CUDA-core, 2 tcgen05 1-CTA, 3 tcgen05 CTA-pair).
  * which = 1: CTAs used by the scan (0 = one per SM).
- * which = 2: developer switches (0 in production).
+ * which = 2: developer switches of the scan kernel; they exist only in a -DPILOTT_DEBUG build, the
+ *            production library answers PILOTT_EUNSUPPORTED to any value but 0.
  * which = 3: candidates each partial list keeps: 0 auto (8 when k <= 10 and the pair scan produces >= 16 lists per query; 16 when k <= 12 or >= 8 lists; else 32), 8, 16, 32.
  * which = 4: 1 = record CUDA events around the scan kernel (read with pilott_mem_profile_read).
  * which = 5 / 6: reported index = sequence * stride (5) + offset (6); a row-sharded store that
  *            holds global rows i with i % world == rank uses stride = world, offset = rank.
  * which = 7: set `total` (rows ever appended, >= rows held): a restored snapshot continues the
  *            sequence numbering of the store it was taken from.
- * which = 8: survivors finish_kernel re-scores exactly per query: 0 auto (32), 16 (applies when k <= 12), 32.
- * which = 9: form of the finish step: 0 one kernel, 1 split into a merge kernel and a re-score kernel. */
+ * which = 9: form of the finish step: 0 selective (re-scores only the survivors that can reach the
+ *            top-k and lets the gap check prove the cut; default), 1 the original kernel that
+ *            re-scores all 32 survivors.  Same results. */
 int pilott_mem_set_option(pilott_mem_t* h, int which, int64_t value);
 /* Kernel launches enqueued by this handle since creation (bench bookkeeping). */
 int64_t pilott_mem_launch_count(const pilott_mem_t* h);
@@ -181,8 +191,10 @@ int pilott_mem_search_refine(pilott_mem_t* h, const float* q_dev, int64_t nq, co
  * Limit: round_up(nq * row_stride * 2, 256) + nsel * rows_held * 8 <= PILOTT_NOALLOC_SCRATCH_BYTES
  * (e.g. 20 selected queries against 100 000 rows), and nsel <= 65535; beyond that the call
  * fails with PILOTT_EINVAL and a message that states both numbers.
- * First call on each device looks up the array's device address (cudaGetSymbolAddress) and
- * caches it; make that first call before starting any stream capture.
+ * Set-up (the lookup of the array's device address with cudaGetSymbolAddress, which is also what
+ * makes CUDA load the library's device image -- array included -- on that device) happens once
+ * per device inside pilott_mem_create, never in this call; create your handles before starting
+ * any stream capture.
  * The array is shared by every call on the device and keeps the previous call's contents.
  * Nothing in it needs to start at zero (each call rewrites what it reads), but two calls that
  * overlap on the GPU -- different streams or different handles on one device -- race on it:

@@ -142,10 +142,16 @@ struct pilott_mem {
     int64_t* expires = nullptr;
     float* scale = nullptr;
     float* tile_max = nullptr;
-    DevBuf qbuf, partials, gthr, exact_scratch, stage_dev, result_dev, misc_dev, refine, result_ids, largek, surv;
+    DevBuf qbuf, partials, gthr, exact_scratch, stage_dev, result_dev, misc_dev, refine, result_ids, largek;
     HostBuf stage_host;
     cudaStream_t own_stream = nullptr;
     cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;   // copy streams of the pipelined host path
+    // Ordering between the two families of entry points, which share the handle's scratch and
+    // columns: device-pointer calls enqueue on the CALLER's stream, host-buffer calls on own_stream.
+    // ev_dev is recorded behind every device-pointer call, ev_own behind every host-buffer call that
+    // returns without synchronising; each family waits for the other's last event before it enqueues.
+    cudaEvent_t ev_dev = nullptr, ev_own = nullptr;
+    bool dev_pending = false, own_pending = false;
     HostSlot hslot[HOST_SLOTS];
     CUtensorMap map_c;
     bool tc_ok = false;
@@ -153,8 +159,7 @@ struct pilott_mem {
     int opt_ctas = 0;
     int opt_dbg = 0;
     int opt_list_len = 0;   // 0 auto, 8, 16, 32
-    int opt_pool = 0;       // 0 auto (32), 16, 32: survivors finish_kernel re-scores
-    int opt_finish = 0;     // 0 one kernel, 1 split (merge kernel + re-score kernel)
+    int opt_finish = 0;     // 0 selective re-score (default), 1 the original kernel that re-scores all 32 survivors
     int auto_min_list = 8;  // floor of the automatic list length: raised when searches keep flagging queries
     int64_t searches_since_refine = 0;
     int64_t seq_mul = 1, seq_add = 0;   // reported index = seq * seq_mul + seq_add (row-sharded stores)
@@ -162,6 +167,7 @@ struct pilott_mem {
     std::vector<cudaEvent_t> ev;        // pairs: [2i] before, [2i+1] after
     size_t ev_used = 0;
     int64_t launches = 0;
+    int64_t generation = 0; // bumped by everything that changes which rows are held (append, clear, compact)
 };
 
 // Exchange buffers of one rank of a row-sharded store (xchg.cu).
@@ -179,6 +185,26 @@ struct pilott_xchg {
 namespace {
 
 int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
+
+// Called at the top of every device-pointer entry point: work this handle still has in flight on
+// its own stream (pilott_mem_search_host_begin) must finish before `st` touches the shared scratch.
+int order_device_call(pilott_mem* h, cudaStream_t st) {
+    if (h->own_pending) CK(cudaStreamWaitEvent(st, h->ev_own, 0));
+    return PILOTT_OK;
+}
+// ... and at its end: remember where the work went.
+int note_device_call(pilott_mem* h, cudaStream_t st) {
+    CK(cudaEventRecord(h->ev_dev, st));
+    h->dev_pending = true;
+    return PILOTT_OK;
+}
+// Called at the top of every host-buffer entry point: own_stream waits for the last device-pointer
+// call (an append whose rows the search must see, a search still using qbuf / scale / partials).
+int order_host_call(pilott_mem* h) {
+    if (h->dev_pending) CK(cudaStreamWaitEvent(h->own_stream, h->ev_dev, 0));
+    h->dev_pending = false;          // own_stream is now ordered behind it, and so is everything enqueued there later
+    return PILOTT_OK;
+}
 
 void free_columns(pilott_mem* h) {
     cudaFree(h->vec); cudaFree(h->inv_norm); cudaFree(h->prio); cudaFree(h->tagmask);
@@ -316,8 +342,7 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
         if (e1) CK(cudaEventRecord(e1, st));
     }
     f.partials = a.partials; f.slots = lists; f.list_len = a.list_len; f.qb = h->qbuf.p; f.vec = h->vec; f.ld = h->ld;
-    // survivors re-scored exactly: 32 (a wide margin below the k-th keeps the gap check quiet), or what option 8 says
-    f.pool_n = (h->opt_pool == 16 && k <= 12) ? 16 : 32;
+    f.pool_n = 32;
     f.nq = nq; f.capacity = h->capacity; f.head = h->head; f.base_seq = h->total - h->count;
     f.k = k; f.seq_mul = h->seq_mul; f.seq_add = h->seq_add;
     f.err = h->ld * 2.4e-7 > 1e-4 ? h->ld * 2.4e-7 : 1e-4;
@@ -327,13 +352,9 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
         f.peers = x->peers_dev; f.world = x->world; f.rank = x->rank; f.block_bytes = x->block_bytes;
         f.flags_off = x->flags_off; f.step = step; f.done_counter = x->done_dev;
     }
-    if (h->opt_finish == 1) {
-        rc = h->surv.ensure((size_t)nq * 33 * 8);
-        if (rc) return rc;
-        f.surv = (uint64_t*)h->surv.p;
-    }
+    f.legacy = h->opt_finish == 1;
     CK(pilott::launch_finish(f, st));
-    h->launches += f.surv ? 3 : 2;
+    h->launches += 2;
     return PILOTT_OK;
 }
 
@@ -585,6 +606,24 @@ int largek_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
     return PILOTT_OK;
 }
 
+// Device address of g_noalloc_scratch on `device` (which must be the current device).  The
+// lookup runs once per device; later calls return the cached pointer.
+constexpr int kNoallocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+void* g_noalloc_ptr[kNoallocMaxDevices] = {};
+
+int noalloc_scratch(int device, unsigned char** out) {
+    if (device < 0 || device >= kNoallocMaxDevices) return fail(PILOTT_EINVAL, "device index out of range");
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[device]) {
+        void* ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch);
+        if (e != cudaSuccess) return fail_cuda(e, "cudaGetSymbolAddress(g_noalloc_scratch)");
+        g_noalloc_ptr[device] = ptr;
+    }
+    *out = static_cast<unsigned char*>(g_noalloc_ptr[device]);
+    return PILOTT_OK;
+}
 }  // namespace
 
 extern "C" int pilott_kp(void) { return 32; }
@@ -615,11 +654,31 @@ int pilott_mem_create(int dim, int64_t capacity, int device, pilott_mem_t** out)
         cudaError_t e = cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking);
         if (e != cudaSuccess) rc = fail_cuda(e, "cudaStreamCreate");
     }
+    if (rc == PILOTT_OK) {
+        cudaError_t e = cudaEventCreateWithFlags(&h->ev_dev, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_own, cudaEventDisableTiming);
+        if (e != cudaSuccess) rc = fail_cuda(e, "cudaEventCreate");
+    }
     if (rc == PILOTT_OK && h->tc_ok) {
         cudaError_t e = pilott::scan_tc_init();
         if (e != cudaSuccess) { h->tc_ok = false; cudaGetLastError(); }
     }
-    if (rc != PILOTT_OK) { free_columns(h); delete h; return rc; }
+    if (rc == PILOTT_OK) {
+        // Set-up of pilott_mem_search_exact_noalloc for this device, done HERE so that the entry
+        // point itself never triggers it: with CUDA's lazy module loading the library's device
+        // image -- and the 16 MiB backing g_noalloc_scratch -- is only loaded on a device when one of
+        // its symbols is first used there, and that load allocates.  create() allocates anyway.
+        unsigned char* unused = nullptr;
+        rc = noalloc_scratch(device, &unused);
+    }
+    if (rc != PILOTT_OK) {
+        free_columns(h);
+        if (h->own_stream) cudaStreamDestroy(h->own_stream);
+        if (h->ev_dev) cudaEventDestroy(h->ev_dev);
+        if (h->ev_own) cudaEventDestroy(h->ev_own);
+        delete h;
+        return rc;
+    }
     CK(cudaDeviceSynchronize());
     if (const char* f = getenv("PILOTT_FINISH_FORM")) h->opt_finish = atoi(f) == 1 ? 1 : 0;   // developer switch (option 9)
     *out = h;
@@ -632,7 +691,7 @@ int pilott_mem_destroy(pilott_mem_t* h) {
     cudaDeviceSynchronize();
     free_columns(h);
     h->qbuf.release(); h->partials.release(); h->gthr.release(); h->exact_scratch.release(); h->stage_dev.release();
-    h->result_dev.release(); h->misc_dev.release(); h->refine.release(); h->result_ids.release(); h->largek.release(); h->surv.release();
+    h->result_dev.release(); h->misc_dev.release(); h->refine.release(); h->result_ids.release(); h->largek.release();
     h->stage_host.release();
     for (cudaEvent_t e : h->ev) cudaEventDestroy(e);
     for (auto& sl : h->hslot) {
@@ -644,6 +703,8 @@ int pilott_mem_destroy(pilott_mem_t* h) {
     if (h->h2d_stream) cudaStreamDestroy(h->h2d_stream);
     if (h->d2h_stream) cudaStreamDestroy(h->d2h_stream);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
+    if (h->ev_dev) cudaEventDestroy(h->ev_dev);
+    if (h->ev_own) cudaEventDestroy(h->ev_own);
     delete h;
     return PILOTT_OK;
 }
@@ -652,6 +713,7 @@ int pilott_mem_clear(pilott_mem_t* h, void* stream) {
     if (!h) return fail(PILOTT_EINVAL, "handle is NULL");
     (void)stream;
     h->total = 0; h->count = 0; h->head = 0;
+    ++h->generation;
     return PILOTT_OK;
 }
 
@@ -692,11 +754,14 @@ int pilott_mem_set_option(pilott_mem_t* h, int which, int64_t value) {
     } else if (which == 9) {
         if (value != 0 && value != 1) return fail(PILOTT_EINVAL, "finish form must be 0 or 1");
         h->opt_finish = (int)value;
-    } else if (which == 8) {
-        if (value != 0 && value != 16 && value != 32) return fail(PILOTT_EINVAL, "survivor count must be 0, 16 or 32");
-        h->opt_pool = (int)value;
     } else if (which == 2) {
+#ifdef PILOTT_DEBUG
         h->opt_dbg = (int)value;      // developer switches (profiling experiments); 0 = off
+#else
+        if (value != 0)
+            return fail(PILOTT_EUNSUPPORTED, "developer switches exist only in -DPILOTT_DEBUG builds of the library");
+        h->opt_dbg = 0;
+#endif
     } else {
         return fail(PILOTT_EINVAL, "unknown option");
     }
@@ -721,15 +786,10 @@ int pilott_mem_profile_read(pilott_mem_t* h, double* scan_ms_total, int64_t* n_s
     return PILOTT_OK;
 }
 
-int pilott_mem_append(pilott_mem_t* h, const float* x_dev, int64_t n, const int32_t* prio_dev,
-                      const uint64_t* tagmask_dev, const int64_t* expires_us_dev, int64_t* first_seq,
-                      void* stream) {
-    if (!h) return fail(PILOTT_EINVAL, "handle is NULL");
-    if (n < 0 || n > h->capacity) return fail(PILOTT_EINVAL, "append batch must hold between 0 and capacity rows");
+static int append_core(pilott_mem_t* h, const float* x_dev, int64_t n, const int32_t* prio_dev,
+                       const uint64_t* tagmask_dev, const int64_t* expires_us_dev, int64_t* first_seq,
+                       void* stream) {
     if (first_seq) *first_seq = h->total;
-    if (n == 0) return PILOTT_OK;
-    if (!x_dev) return fail(PILOTT_EINVAL, "x is NULL");
-    DeviceGuard g(h->device);
     int64_t first_slot = h->head + h->count;
     if (first_slot >= h->capacity) first_slot -= h->capacity;
     CK(pilott::launch_append(x_dev, n, h->dim, h->ld, h->vec, h->inv_norm, h->prio, h->tagmask, h->expires,
@@ -741,7 +801,23 @@ int pilott_mem_append(pilott_mem_t* h, const float* x_dev, int64_t n, const int3
     if (over > 0) { h->head = (h->head + over) % h->capacity; h->count = h->capacity; }
     else h->count += n;
     h->total += n;
+    ++h->generation;
     return PILOTT_OK;
+}
+
+int pilott_mem_append(pilott_mem_t* h, const float* x_dev, int64_t n, const int32_t* prio_dev,
+                      const uint64_t* tagmask_dev, const int64_t* expires_us_dev, int64_t* first_seq,
+                      void* stream) {
+    if (!h) return fail(PILOTT_EINVAL, "handle is NULL");
+    if (n < 0 || n > h->capacity) return fail(PILOTT_EINVAL, "append batch must hold between 0 and capacity rows");
+    if (n == 0) { if (first_seq) *first_seq = h->total; return PILOTT_OK; }
+    if (!x_dev) return fail(PILOTT_EINVAL, "x is NULL");
+    DeviceGuard g(h->device);
+    int rc = order_device_call(h, (cudaStream_t)stream);
+    if (rc) return rc;
+    rc = append_core(h, x_dev, n, prio_dev, tagmask_dev, expires_us_dev, first_seq, stream);
+    if (rc) return rc;
+    return note_device_call(h, (cudaStream_t)stream);
 }
 
 int pilott_mem_append_host(pilott_mem_t* h, const float* x_host, int64_t n, const int32_t* prio_host,
@@ -766,12 +842,15 @@ int pilott_mem_append_host(pilott_mem_t* h, const float* x_host, int64_t n, cons
     if (tagmask_host) memcpy(hs + off_t, tagmask_host, tb);
     if (expires_us_host) memcpy(hs + off_e, expires_us_host, eb);
     cudaStream_t st = h->own_stream;
+    rc = order_host_call(h);
+    if (rc) return rc;
     CK(cudaMemcpyAsync(ds, hs, tot, cudaMemcpyHostToDevice, st));
-    rc = pilott_mem_append(h, (const float*)ds, n, prio_host ? (const int32_t*)(ds + off_p) : nullptr,
+    rc = append_core(h, (const float*)ds, n, prio_host ? (const int32_t*)(ds + off_p) : nullptr,
                            tagmask_host ? (const uint64_t*)(ds + off_t) : nullptr,
                            expires_us_host ? (const int64_t*)(ds + off_e) : nullptr, first_seq, st);
     if (rc) return rc;
     CK(cudaStreamSynchronize(st));
+    h->own_pending = false;
     return PILOTT_OK;
 }
 
@@ -783,8 +862,12 @@ int pilott_mem_search(pilott_mem_t* h, const float* q_dev, int64_t nq, int k, in
     if (nq < 0) return fail(PILOTT_EINVAL, "nq is negative");
     if (nq > 0 && (!q_dev || !out_idx_dev || !out_score_dev)) return fail(PILOTT_EINVAL, "NULL query or output pointer");
     DeviceGuard g(h->device);
-    return search_core(h, q_dev, nq, k, min_prio, req_tagmask, now_us, out_idx_dev, out_score_dev,
-                       out_score64_dev, out_inexact_dev, out_flags_dev, (cudaStream_t)stream);
+    int rc = order_device_call(h, (cudaStream_t)stream);
+    if (rc) return rc;
+    rc = search_core(h, q_dev, nq, k, min_prio, req_tagmask, now_us, out_idx_dev, out_score_dev,
+                     out_score64_dev, out_inexact_dev, out_flags_dev, (cudaStream_t)stream);
+    if (rc) return rc;
+    return note_device_call(h, (cudaStream_t)stream);
 }
 
 int pilott_mem_search_exact(pilott_mem_t* h, const float* q_dev, int64_t nq, const int32_t* query_ids_dev,
@@ -795,8 +878,12 @@ int pilott_mem_search_exact(pilott_mem_t* h, const float* q_dev, int64_t nq, con
     if (nq < 0) return fail(PILOTT_EINVAL, "nq is negative");
     if (nq > 0 && (!q_dev || !out_idx_dev || !out_score_dev)) return fail(PILOTT_EINVAL, "NULL query or output pointer");
     DeviceGuard g(h->device);
-    return exact_core(h, q_dev, nq, query_ids_dev, nsel, k, min_prio, req_tagmask, now_us, out_idx_dev,
-                      out_score_dev, out_score64_dev, (cudaStream_t)stream);
+    int rc = order_device_call(h, (cudaStream_t)stream);
+    if (rc) return rc;
+    rc = exact_core(h, q_dev, nq, query_ids_dev, nsel, k, min_prio, req_tagmask, now_us, out_idx_dev,
+                    out_score_dev, out_score64_dev, (cudaStream_t)stream);
+    if (rc) return rc;
+    return note_device_call(h, (cudaStream_t)stream);
 }
 
 int pilott_mem_search_refine(pilott_mem_t* h, const float* q_dev, int64_t nq, const int32_t* query_ids_dev,
@@ -807,8 +894,12 @@ int pilott_mem_search_refine(pilott_mem_t* h, const float* q_dev, int64_t nq, co
     if (nq < 0) return fail(PILOTT_EINVAL, "nq is negative");
     if (nq > 0 && (!q_dev || !out_idx_dev || !out_score_dev)) return fail(PILOTT_EINVAL, "NULL query or output pointer");
     DeviceGuard g(h->device);
-    return refine_core(h, q_dev, nq, query_ids_dev, nsel, k, min_prio, req_tagmask, now_us, out_idx_dev,
-                       out_score_dev, out_score64_dev, n_bruteforce, (cudaStream_t)stream);
+    int rc = order_device_call(h, (cudaStream_t)stream);
+    if (rc) return rc;
+    rc = refine_core(h, q_dev, nq, query_ids_dev, nsel, k, min_prio, req_tagmask, now_us, out_idx_dev,
+                     out_score_dev, out_score64_dev, n_bruteforce, (cudaStream_t)stream);
+    if (rc) return rc;
+    return note_device_call(h, (cudaStream_t)stream);
 }
 
 int pilott_mem_search_large(pilott_mem_t* h, const float* q_dev, int64_t nq, int k, int32_t min_prio,
@@ -819,8 +910,12 @@ int pilott_mem_search_large(pilott_mem_t* h, const float* q_dev, int64_t nq, int
     if (k < 1) return fail(PILOTT_EINVAL, "k must be >= 1");
     if (nq > 0 && (!q_dev || !out_idx_dev || !out_score_dev)) return fail(PILOTT_EINVAL, "NULL query or output pointer");
     DeviceGuard g(h->device);
-    return largek_core(h, q_dev, nq, k, min_prio, req_tagmask, now_us, out_idx_dev, out_score_dev, out_score64_dev,
-                       n_bruteforce, (cudaStream_t)stream);
+    int rc = order_device_call(h, (cudaStream_t)stream);
+    if (rc) return rc;
+    rc = largek_core(h, q_dev, nq, k, min_prio, req_tagmask, now_us, out_idx_dev, out_score_dev, out_score64_dev,
+                     n_bruteforce, (cudaStream_t)stream);
+    if (rc) return rc;
+    return note_device_call(h, (cudaStream_t)stream);
 }
 
 int pilott_mem_search_host(pilott_mem_t* h, const float* q_host, int64_t nq, int k, int32_t min_prio,
@@ -844,6 +939,8 @@ int pilott_mem_search_host(pilott_mem_t* h, const float* q_host, int64_t nq, int
     rc = h->stage_dev.ensure(qb);
     if (rc) return rc;
     rc = h->result_dev.ensure(rtot);
+    if (rc) return rc;
+    rc = order_host_call(h);
     if (rc) return rc;
     if (is_pinned(q_host)) {          // caller's buffer is page-locked: DMA straight from it
         CK(cudaMemcpyAsync(h->stage_dev.p, q_host, qb, cudaMemcpyHostToDevice, st));
@@ -889,6 +986,7 @@ int pilott_mem_search_host(pilott_mem_t* h, const float* q_host, int64_t nq, int
     memcpy(out_idx_host, rh, ib);
     memcpy(out_score_host, rh + off_s, sb);
     if (out_score64_host) memcpy(out_score64_host, rh + off_s64, s64b);
+    h->own_pending = false;           // own_stream was synchronised above
     return PILOTT_OK;
 }
 
@@ -929,6 +1027,8 @@ int pilott_mem_search_host_begin(pilott_mem_t* h, int slot, const float* q_host,
     CK(cudaMemcpyAsync(sl.q_dev.p, src, qb, cudaMemcpyHostToDevice, h->h2d_stream));
     CK(cudaEventRecord(sl.e_h2d, h->h2d_stream));
     cudaStream_t st = h->own_stream;
+    rc = order_host_call(h);
+    if (rc) return rc;
     CK(cudaStreamWaitEvent(st, sl.e_h2d, 0));
     char* rd = (char*)sl.res_dev.p;
     sl.nq = nq; sl.k = k; sl.min_prio = min_prio; sl.req = req_tagmask; sl.now_us = now_us;
@@ -942,6 +1042,8 @@ int pilott_mem_search_host_begin(pilott_mem_t* h, int slot, const float* q_host,
                          (float*)(rd + sl.off_s), (double*)(rd + sl.off_s64), &sl.n_brute, st);
     if (rc) return rc;
     CK(cudaEventRecord(sl.e_done, st));
+    CK(cudaEventRecord(h->ev_own, st));
+    h->own_pending = true;            // a device-pointer call that follows waits for this search
     CK(cudaStreamWaitEvent(h->d2h_stream, sl.e_done, 0));
     CK(cudaMemcpyAsync(sl.res_host.p, rd, sl.rtot, cudaMemcpyDeviceToHost, h->d2h_stream));
     CK(cudaEventRecord(sl.e_d2h, h->d2h_stream));
@@ -1011,24 +1113,42 @@ int pilott_mem_compact(pilott_mem_t* h, int64_t now_us, int64_t* kept, uint8_t* 
     if (kept) *kept = m;
     h->launches += 1;
     if (m == n) return PILOTT_OK;
-    // gather the survivors into fresh columns, then swap
-    pilott_mem old = *h;
-    h->vec = nullptr; h->inv_norm = nullptr; h->prio = nullptr; h->tagmask = nullptr;
-    h->expires = nullptr; h->scale = nullptr; h->tile_max = nullptr;
-    rc = alloc_columns(h);
-    if (rc) { free_columns(h); *h = old; return rc; }
+    // Gather the survivors into fresh columns, then swap.  (Needs room for a second copy of the
+    // columns while it runs; a store that fills more than half of HBM cannot be compacted this way.)
+    // Everything that can fail is done before the handle is touched, and any failure after the
+    // new columns exist frees them and puts the old ones back, so an error leaves the store as it was.
     if (m > 0) {
         rc = h->stage_dev.ensure((size_t)m * 8);
         if (rc) return rc;
         CK(cudaMemcpyAsync(h->stage_dev.p, src.data(), (size_t)m * 8, cudaMemcpyHostToDevice, st));
-        CK(pilott::launch_gather_rows(old.vec, old.inv_norm, old.prio, old.tagmask, old.expires, h->ld,
-                                      (const int64_t*)h->stage_dev.p, m, h->vec, h->inv_norm, h->prio,
-                                      h->tagmask, h->expires, st));
+        CK(cudaStreamSynchronize(st));          // src is a host vector
+    }
+    struct Columns {
+        void* vec; float* inv_norm; int32_t* prio; uint64_t* tagmask; int64_t* expires; float* scale; float* tile_max;
+        CUtensorMap map_c; bool tc_ok;
+    };
+    const Columns old{h->vec, h->inv_norm, h->prio, h->tagmask, h->expires, h->scale, h->tile_max, h->map_c, h->tc_ok};
+    auto restore = [&]() {
+        free_columns(h);
+        h->vec = old.vec; h->inv_norm = old.inv_norm; h->prio = old.prio; h->tagmask = old.tagmask;
+        h->expires = old.expires; h->scale = old.scale; h->tile_max = old.tile_max; h->map_c = old.map_c; h->tc_ok = old.tc_ok;
+    };
+    h->vec = nullptr; h->inv_norm = nullptr; h->prio = nullptr; h->tagmask = nullptr;
+    h->expires = nullptr; h->scale = nullptr; h->tile_max = nullptr;
+    rc = alloc_columns(h);
+    if (rc) { restore(); return rc; }
+    if (m > 0) {
+        cudaError_t e = pilott::launch_gather_rows(old.vec, old.inv_norm, old.prio, old.tagmask, old.expires, h->ld,
+                                                   (const int64_t*)h->stage_dev.p, m, h->vec, h->inv_norm, h->prio,
+                                                   h->tagmask, h->expires, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) { restore(); return fail_cuda(e, "pilott_mem_compact: gather of the surviving rows"); }
         h->launches += 1;
     }
-    CK(cudaStreamSynchronize(st));
-    free_columns(&old);
+    cudaFree(old.vec); cudaFree(old.inv_norm); cudaFree(old.prio); cudaFree(old.tagmask);
+    cudaFree(old.expires); cudaFree(old.scale); cudaFree(old.tile_max);
     h->head = 0; h->count = m;       // total is unchanged: survivors are re-based to total-m+age
+    ++h->generation;
     return PILOTT_OK;
 }
 
@@ -1147,8 +1267,12 @@ int pilott_mem_search_publish(pilott_mem_t* h, pilott_xchg_t* x, int64_t step, c
     if (2 * nq * k * 8 > x->block_bytes) return fail(PILOTT_EINVAL, "[2, nq, k] block exceeds block_bytes");
     if (!q_dev || !out_idx_dev || !out_score_dev) return fail(PILOTT_EINVAL, "NULL query or output pointer");
     DeviceGuard g(h->device);
-    return search_core(h, q_dev, nq, k, min_prio, req_tagmask, now_us, out_idx_dev, out_score_dev,
-                       out_score64_dev, out_inexact_dev, out_flags_dev, (cudaStream_t)stream, x, step);
+    int rc = order_device_call(h, (cudaStream_t)stream);
+    if (rc) return rc;
+    rc = search_core(h, q_dev, nq, k, min_prio, req_tagmask, now_us, out_idx_dev, out_score_dev,
+                     out_score64_dev, out_inexact_dev, out_flags_dev, (cudaStream_t)stream, x, step);
+    if (rc) return rc;
+    return note_device_call(h, (cudaStream_t)stream);
 }
 
 int pilott_xchg_publish(pilott_xchg_t* x, const void* block_dev, int64_t bytes, int64_t step, void* stream) {
@@ -1226,27 +1350,6 @@ int pilott_task_priority(const uint8_t* urgent_dev, const int32_t* complexity_de
     return PILOTT_OK;
 }
 
-// Device address of g_noalloc_scratch on `device` (which must be the current device).  The
-// lookup runs once per device; later calls return the cached pointer.
-namespace {
-constexpr int kNoallocMaxDevices = 64;
-std::mutex g_noalloc_mu;
-void* g_noalloc_ptr[kNoallocMaxDevices] = {};
-
-int noalloc_scratch(int device, unsigned char** out) {
-    if (device < 0 || device >= kNoallocMaxDevices) return fail(PILOTT_EINVAL, "device index out of range");
-    std::lock_guard<std::mutex> lk(g_noalloc_mu);
-    if (!g_noalloc_ptr[device]) {
-        void* ptr = nullptr;
-        cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch);
-        if (e != cudaSuccess) return fail_cuda(e, "cudaGetSymbolAddress(g_noalloc_scratch)");
-        g_noalloc_ptr[device] = ptr;
-    }
-    *out = static_cast<unsigned char*>(g_noalloc_ptr[device]);
-    return PILOTT_OK;
-}
-}  // namespace
-
 int pilott_mem_search_exact_noalloc(pilott_mem_t* h, const float* q_dev, int64_t nq,
                                     const int32_t* query_ids_dev, int64_t nsel, int k, int32_t min_prio,
                                     uint64_t req_tagmask, int64_t now_us, int64_t* out_idx_dev,
@@ -1269,9 +1372,11 @@ int pilott_mem_search_exact_noalloc(pilott_mem_t* h, const float* q_dev, int64_t
                     "pilott_mem_search_exact, which allocates");
     DeviceGuard g(h->device);
     unsigned char* scratch = nullptr;
-    int rc = noalloc_scratch(h->device, &scratch);      // first call on this device: symbol lookup
+    int rc = noalloc_scratch(h->device, &scratch);      // cached by pilott_mem_create: no lookup, no module load here
     if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
+    rc = order_device_call(h, st);
+    if (rc) return rc;
     // Nothing in the buffer has to start at zero: the query block and every score the selection
     // reads are rewritten by the two kernels below before they are read.
     CK(pilott::launch_convert_queries(q_dev, nq, h->dim, h->ld, scratch, st));
@@ -1279,8 +1384,8 @@ int pilott_mem_search_exact_noalloc(pilott_mem_t* h, const float* q_dev, int64_t
                             h->head, h->total - h->count, h->seq_mul, h->seq_add, query_ids_dev, nsel, k,
                             min_prio, req_tagmask, now_us, reinterpret_cast<double*>(scratch + q_bytes),
                             out_idx_dev, out_score_dev, out_score64_dev, st));
-    h->launches += 3;
-    return PILOTT_OK;
+    h->launches += h->count > 0 ? 3 : 2;                // convert, [scores,] select
+    return note_device_call(h, st);
 }
 
 }  // extern "C"

@@ -336,51 +336,79 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_l
 }
 
 // ---------------------------------------------------------------------------------------
-// The same finish in two kernels (FinishArgs::split).  finish_kernel is bound by dependent
-// latencies at 4 CTAs of 124 registers per SM; split, the merge runs one WARP per query (every
-// query of a 1024-batch resident at once) and the re-score stages 16 rows at a time and gives
-// each lane ONE partial sum, so 7 CTAs fit an SM and the batch takes one wave.
+// finish_sel_kernel -- the default finish step.  Same inputs, same outputs and the same proof as
+// finish_kernel above, but it re-scores only the survivors that CAN be in the top-k.
+//
+// finish_kernel re-scores all 32 survivors of every query with lane = survivor, so its cost is set
+// by the 768-element fp64 chain of a full warp (and by the bf16 -> fp64 conversions: F2F.F64.F32
+// issues at a quarter of the DFMA rate and every lane converted the same query element).  Here:
+//   * the 32 survivors come out of the merge sorted by approximate score a_0 >= a_1 >= ...; with
+//     |exact - approximate| <= err (the bound the gap check already relies on) the exact k-th best
+//     is >= a_{k-1} - err, so a survivor with a_i < a_{k-1} - 2 err cannot be in the top-k.  Only
+//     the R survivors above that line are fetched and re-scored (k = 10 on random data: R = 11..13
+//     instead of 32: a third of the gather traffic and of the fp64 work);
+//   * nothing is taken on trust: the best survivor that was NOT re-scored joins `bound`, and the
+//     gap check (bound + err < exact k-th) proves the cut like it proves every other drop -- a
+//     query it cannot prove is flagged and goes to the second-chance pass as before;
+//   * work is spread as thread = (survivor, partial sum): 16 survivors x the 8 interleaved partial
+//     sums of the stated rule per round of 128 threads, so a round costs ld/8 iterations of
+//     {LDS.64 query (pre-converted to fp64 once per CTA), LDS.U16 row, one F2F, two DFMA}; the
+//     query norm is accumulated once (survivor 0's threads), not once per survivor;
+//   * the list length is a template parameter (no integer divisions, a fraction of the code).
+// Scores and indices are bit-identical to finish_kernel's whenever the query is not flagged.
 // ---------------------------------------------------------------------------------------
-constexpr int SURV_WORDS = 33;            // per query: 32 survivor keys (descending) + the bound
+constexpr int SEL_ROWS = 16;              // survivors staged and re-scored per round
 
-__global__ void __launch_bounds__(128)
-merge_lists_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_len, int pool_n, int rows_per_group,
-                   int lists_base, int groups_rem, int lists_extra, int64_t nq, const uint32_t* __restrict__ gthr,
-                   uint64_t* __restrict__ surv) {
-    const int lane = threadIdx.x & 31;
-    const int64_t q = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (q >= nq) return;
-    const int per_load = 32 / list_len;
-    const int slots = lists_base + ((q / rows_per_group) < groups_rem ? lists_extra : 0);
-    const uint64_t* p = partials + q * (int64_t)slots_alloc * list_len;
-    const int nloads = (slots + per_load - 1) / per_load;
+template <int LL>
+__global__ void __launch_bounds__(FIN_WARPS * 32, 6)
+finish_sel_kernel(const __grid_constant__ FinishArgs a) {
+    extern __shared__ __align__(16) unsigned char s_dyn[];      // [ld] fp64 query | [ld] bf16 query | [SEL_ROWS][ld*2+16] rows
+    __shared__ uint64_t s_pool[FIN_WARPS][32];
+    __shared__ uint64_t s_bound[FIN_WARPS];
+    __shared__ double s_dot[32], s_nm[32];
+    __shared__ double s_nq;
+    __shared__ int s_R;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, tid = threadIdx.x;
+    const int64_t q = blockIdx.x;
+    const int ld = a.ld, k = a.k;
+    double* q64 = reinterpret_cast<double*>(s_dyn);
+    unsigned char* q16 = s_dyn + (size_t)ld * 8;
+    unsigned char* rows = q16 + (size_t)ld * 2;
+    const size_t row_bytes = (size_t)ld * 2 + 16;               // +16: consecutive rows start 4 banks apart
+    const __nv_bfloat16* qb = reinterpret_cast<const __nv_bfloat16*>(a.qb);
+    const __nv_bfloat16* vec = reinterpret_cast<const __nv_bfloat16*>(a.vec);
+    const int chunks = ld / 8;                                  // 16-byte pieces per row
+
+    // 0. the query row is on its way while the lists are merged
+    for (int c = tid; c < chunks; c += FIN_WARPS * 32) cp_async16(q16 + 16 * c, qb + q * ld + 8 * c);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+
+    // 1. top-32 of this warp's lists by approximate key; `bound` = best key NOT kept (see finish_kernel)
+    constexpr int PER = 32 / LL;                                // lists per 32-lane load
+    const int slots = a.lists_base + ((q / a.rows_per_group) < a.groups_rem ? a.lists_extra : 0);
+    const uint64_t* p = a.partials + q * (int64_t)a.slots * LL;
+    const int nloads = (slots + PER - 1) / PER;
+    auto load_keys = [&](int i) -> uint64_t {
+        const int li = i * PER + lane / LL;
+        return (i < nloads && li < slots) ? __ldcg(p + (int64_t)li * LL + (lane % LL)) : 0ull;
+    };
     uint64_t best = 0ull, bound = 0ull, drop = 0ull;
-    for (int i0 = 0; i0 < nloads; i0 += 4) {
-        uint64_t x[4];
+    uint64_t cur = load_keys(warp), nxt = load_keys(warp + FIN_WARPS);
+#pragma unroll 1
+    for (int i = warp; i < nloads; i += FIN_WARPS) {
+        const uint64_t nn = load_keys(i + 2 * FIN_WARPS);       // two loads ahead
+        uint64_t mn = cur;                                      // per-list minimum (segmented butterfly)
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {                      // four loads in flight before any sort
-            const int li = (i0 + u) * per_load + lane / list_len;
-            x[u] = (i0 + u < nloads && li < slots) ? __ldcg(p + (int64_t)li * list_len + (lane % list_len)) : 0ull;
+        for (int j = LL / 2; j > 0; j >>= 1) {
+            const uint64_t o = shfl_xor64(mn, j);
+            mn = mn < o ? mn : o;
         }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            if (i0 + u >= nloads) break;
-            uint64_t mn = x[u];                            // per-list minimum: a FULL list may have dropped rows <= it
-            for (int j = list_len / 2; j > 0; j >>= 1) {
-                const uint64_t o = shfl_xor64(mn, j);
-                mn = mn < o ? mn : o;
-            }
-            if (mn != 0ull && mn > bound) bound = mn;
-            const uint64_t xs = warp_sort64<false>(x[u], lane);
-            const uint64_t lo = best < xs ? best : xs;     // the 32 keys this merge drops
-            drop = drop > lo ? drop : lo;
-            best = warp_bitonic_merge_desc(best > xs ? best : xs, lane);
-        }
-    }
-    if (pool_n < 32) {
-        const uint64_t cut = shfl64(best, pool_n);
-        drop = drop > cut ? drop : cut;
-        if (lane >= pool_n) best = 0ull;
+        if (mn != 0ull && mn > bound) bound = mn;               // list is full: it may have dropped rows <= mn
+        const uint64_t xs = warp_sort64<false>(cur, lane);
+        const uint64_t lo = best < xs ? best : xs;              // the 32 keys this merge drops
+        drop = drop > lo ? drop : lo;
+        best = warp_bitonic_merge_desc(best > xs ? best : xs, lane);
+        cur = nxt; nxt = nn;
     }
     bound = bound > drop ? bound : drop;
 #pragma unroll
@@ -388,116 +416,159 @@ merge_lists_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int l
         const uint64_t o = shfl_xor64(bound, j);
         bound = bound > o ? bound : o;
     }
-    if (gthr) {                                            // rows dropped by a threshold scored below it
-        const uint32_t g = __ldcg(gthr + q);
-        const uint64_t gk = ((uint64_t)g << 32) | 0xFFFFFFFFull;
-        if (g != 0u && gk > bound) bound = gk;
-    }
-    surv[q * SURV_WORDS + lane] = best;
-    if (lane == 0) surv[q * SURV_WORDS + 32] = bound;
-}
+    s_pool[warp][lane] = best;
+    if (lane == 0) s_bound[warp] = bound;
+    asm volatile("cp.async.wait_group 0;" ::: "memory");        // own pieces of the query row have landed
+    __syncthreads();
 
-constexpr int RS_ROWS = 16;               // survivor rows staged per round
-
-__global__ void __launch_bounds__(FIN_WARPS * 32, 7)
-rescore_kernel(const uint64_t* __restrict__ surv, const __nv_bfloat16* __restrict__ qb,
-               const __nv_bfloat16* __restrict__ vec, int ld, int64_t nq, int64_t capacity, int64_t head,
-               int64_t base_seq, int64_t seq_mul, int64_t seq_add, int k, double err, int64_t* __restrict__ out_idx,
-               float* __restrict__ out_score, double* __restrict__ out_score64, uint8_t* __restrict__ flags,
-               int32_t* __restrict__ inexact, unsigned char* const* __restrict__ peers, int world, int rank,
-               int64_t block_bytes, int64_t flags_off, int64_t step, uint32_t* __restrict__ done_counter) {
-    extern __shared__ __align__(16) unsigned char s_rows[];     // [RS_ROWS + 1][ld*2 + 16]: rows of the round, then the query
-    __shared__ double s_part[3][FIN_WARPS][32];                  // pair sums p[2w] + p[2w+1] of (dot, nq, nm) per candidate
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int64_t q = blockIdx.x;
-    const uint64_t key = __ldcg(surv + q * SURV_WORDS + lane);  // lane = candidate (every warp holds all 32)
-    const uint64_t bound = __ldcg(surv + q * SURV_WORDS + 32);
-    const size_t row_bytes = (size_t)ld * 2 + 16;
-    const int chunks = ld / 8;
-    const unsigned char* qrow_s = s_rows + RS_ROWS * row_bytes;
-    const int c = lane & 15, half = lane >> 4;                   // candidate within the round, which partial of the pair
-    for (int round = 0; round < 32 / RS_ROWS; ++round) {
-        if (round) __syncthreads();                              // the previous round's rows are no longer read
-        for (int r = warp; r < RS_ROWS + (round == 0 ? 1 : 0); r += FIN_WARPS) {
-            const __nv_bfloat16* src;
-            if (r == RS_ROWS) src = qb + q * ld;
-            else {
-                const uint64_t kr = __shfl_sync(0xffffffffu, key, round * RS_ROWS + r);
-                if (kr == 0ull) continue;
-                int64_t slot = head + key_age(kr);
-                if (slot >= capacity) slot -= capacity;
-                src = vec + slot * ld;
+    // 2. warp 0: merge the four pools and draw the line; warps 1-3: query -> fp64, once per CTA
+    if (warp == 0) {
+        drop = 0ull;
+#pragma unroll
+        for (int w = 1; w < FIN_WARPS; ++w) {
+            const uint64_t xs = s_pool[w][31 - lane];           // sorted descending; reversed = ascending
+            const uint64_t lo = best < xs ? best : xs;
+            drop = drop > lo ? drop : lo;
+            best = warp_bitonic_merge_desc(best > xs ? best : xs, lane);
+            if (s_bound[w] > bound) bound = s_bound[w];
+        }
+#pragma unroll
+        for (int j = 16; j > 0; j >>= 1) {
+            const uint64_t o = shfl_xor64(drop, j);
+            drop = drop > o ? drop : o;
+        }
+        bound = bound > drop ? bound : drop;
+        if (a.gthr) {                                           // rows dropped by a threshold scored below it
+            const uint32_t g = __ldcg(a.gthr + q);
+            const uint64_t gk = ((uint64_t)g << 32) | 0xFFFFFFFFull;
+            if (g != 0u && gk > bound) bound = gk;
+        }
+        // |q| to fp32 accuracy: it only places the line, the gap check below is what proves the cut
+        float n2 = 0.f;
+        for (int c = lane; c < chunks; c += 32) {
+            const uint4 v = *reinterpret_cast<const uint4*>(q16 + 16 * c);
+            const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float x0 = __uint_as_float(w4[j] << 16), x1 = __uint_as_float(w4[j] & 0xffff0000u);
+                n2 = fmaf(x0, x0, n2);
+                n2 = fmaf(x1, x1, n2);
             }
-            for (int x = lane; x < chunks; x += 32) cp_async16(s_rows + r * row_bytes + 16 * x, src + 8 * x);
+        }
+#pragma unroll
+        for (int j = 16; j > 0; j >>= 1) n2 += __shfl_xor_sync(FULL, n2, j);
+        const int nvalid = __popc(__ballot_sync(FULL, best != 0ull));
+        int R = 0;
+        if (nvalid > 0) {
+            const int kk = (k < nvalid ? k : nvalid) - 1;
+            const float a_k = key_score(shfl64(best, kk));
+            const float line = a_k - 2.0f * (float)a.err * sqrtf(n2) * 1.001f;
+            // keys are sorted by score, so the survivors above the line are lanes [0, R); never fewer than k
+            R = __popc(__ballot_sync(FULL, best != 0ull && !(key_score(best) < line)));
+            if (R <= kk) R = kk + 1;
+        }
+        if (R < nvalid) {                                       // best survivor left out: it bounds the others
+            const uint64_t nb = shfl64(best, R);
+            if (nb > bound) bound = nb;
+        }
+        s_pool[0][lane] = lane < R ? best : 0ull;
+        if (lane == 0) { s_R = R; s_bound[0] = bound; s_nq = 0.0; }
+    } else {
+        for (int d = tid - 32; d < ld; d += (FIN_WARPS - 1) * 32)
+            q64[d] = (double)bf16_bits_to_float(*reinterpret_cast<const uint16_t*>(q16 + 2 * d));
+    }
+    __syncthreads();
+    const int R = s_R;
+
+    // 3. rounds of 16 survivors: gather the rows, then thread (c, j) walks partial sum j of survivor c
+    const int c = tid >> 3, j = tid & 7;
+    for (int r0 = 0; r0 < R; r0 += SEL_ROWS) {
+        const int nr = R - r0 < SEL_ROWS ? R - r0 : SEL_ROWS;
+        for (int r = warp; r < nr; r += FIN_WARPS) {
+            int64_t slot = a.head + key_age(s_pool[0][r0 + r]);
+            if (slot >= a.capacity) slot -= a.capacity;
+            const __nv_bfloat16* src = vec + slot * ld;
+            for (int x = lane; x < chunks; x += 32) cp_async16(rows + r * row_bytes + 16 * x, src + 8 * x);
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
         asm volatile("cp.async.wait_group 0;" ::: "memory");
         __syncthreads();
-        // lane (c, half) accumulates partial sum j = 2*warp + half of the stated rule for candidate
-        // round*16 + c: elements d = j, j+8, ... in ascending order
-        const uint64_t kc = __shfl_sync(0xffffffffu, key, round * RS_ROWS + c);
-        double pd = 0.0, pq = 0.0, pm = 0.0;
-        if (kc != 0ull) {
-            const unsigned char* mrow_s = s_rows + c * row_bytes;
-            const int j = 2 * warp + half;
-            for (int d = j; d < ld; d += 8) {
-                const double qv = (double)__uint_as_float((uint32_t)(*reinterpret_cast<const uint16_t*>(qrow_s + 2 * d)) << 16);
-                const double mv = (double)__uint_as_float((uint32_t)(*reinterpret_cast<const uint16_t*>(mrow_s + 2 * d)) << 16);
-                pd = __fma_rn(qv, mv, pd); pq = __fma_rn(qv, qv, pq); pm = __fma_rn(mv, mv, pm);
+        double pd = 0.0, pm = 0.0, pq = 0.0;
+        if (c < nr) {
+            const unsigned char* mrow = rows + c * row_bytes;
+            if (r0 == 0 && warp == 0) {                         // survivor 0's threads also own |q|^2 (warp-uniform branch)
+#pragma unroll 4
+                for (int d = j; d < ld; d += 8) {
+                    const double qv = q64[d];
+                    const double mv = (double)bf16_bits_to_float(*reinterpret_cast<const uint16_t*>(mrow + 2 * d));
+                    pd = __fma_rn(qv, mv, pd); pm = __fma_rn(mv, mv, pm); pq = __fma_rn(qv, qv, pq);
+                }
+            } else {
+#pragma unroll 4
+                for (int d = j; d < ld; d += 8) {
+                    const double qv = q64[d];
+                    const double mv = (double)bf16_bits_to_float(*reinterpret_cast<const uint16_t*>(mrow + 2 * d));
+                    pd = __fma_rn(qv, mv, pd); pm = __fma_rn(mv, mv, pm);
+                }
             }
         }
-        // p[2w] + p[2w+1]: one rounding, the same sum whichever lane forms it
-        const double sd = __dadd_rn(pd, shfl_xor_d(pd, 16)), sq = __dadd_rn(pq, shfl_xor_d(pq, 16)), sm = __dadd_rn(pm, shfl_xor_d(pm, 16));
-        if (half == 0) {
-            s_part[0][warp][round * RS_ROWS + c] = sd;
-            s_part[1][warp][round * RS_ROWS + c] = sq;
-            s_part[2][warp][round * RS_ROWS + c] = sm;
+        // ((p0+p1)+(p2+p3))+((p4+p5)+(p6+p7)): fp64 addition is commutative, so three butterfly
+        // steps leave exactly that sum in all eight lanes of the survivor
+#pragma unroll
+        for (int s = 1; s < 8; s <<= 1) {
+            pd = __dadd_rn(pd, shfl_xor_d(pd, s));
+            pm = __dadd_rn(pm, shfl_xor_d(pm, s));
+            pq = __dadd_rn(pq, shfl_xor_d(pq, s));
         }
+        if (c < nr && j == 0) {
+            s_dot[r0 + c] = pd; s_nm[r0 + c] = pm;
+            if (r0 == 0 && c == 0) s_nq = pq;
+        }
+        __syncthreads();                                        // results visible; rows free for the next round
     }
-    __syncthreads();
     if (warp != 0) return;
+
+    // 4. scores, final order, outputs, gap check (lane = survivor)
+    const uint64_t key = s_pool[0][lane];
+    bound = s_bound[0];
     const bool pool_full = bound != 0ull;
-    const bool valid = key != 0ull;
-    double sc = -INFINITY, nqn = 0.0;
+    const double nqn = s_nq;
+    double sc = -INFINITY;
     int64_t seq = INT64_MAX;
-    if (valid) {
-        const double dt = __dadd_rn(__dadd_rn(s_part[0][0][lane], s_part[0][1][lane]), __dadd_rn(s_part[0][2][lane], s_part[0][3][lane]));
-        nqn = __dadd_rn(__dadd_rn(s_part[1][0][lane], s_part[1][1][lane]), __dadd_rn(s_part[1][2][lane], s_part[1][3][lane]));
-        const double nmt = __dadd_rn(__dadd_rn(s_part[2][0][lane], s_part[2][1][lane]), __dadd_rn(s_part[2][2][lane], s_part[2][3][lane]));
-        const double den = __dmul_rn(__dsqrt_rn(nqn), __dsqrt_rn(nmt));
-        sc = den > 0.0 ? __ddiv_rn(dt, den) : 0.0;
-        seq = base_seq + key_age(key);
+    if (lane < R) {
+        const double den = __dmul_rn(__dsqrt_rn(nqn), __dsqrt_rn(s_nm[lane]));
+        sc = den > 0.0 ? __ddiv_rn(s_dot[lane], den) : 0.0;
+        seq = a.base_seq + key_age(key);
     }
-    nqn = __longlong_as_double((long long)shfl64((uint64_t)__double_as_longlong(nqn), 0));   // lane 0 is valid whenever pool_full
     warp_sort_pairs(sc, seq, lane);
     if (lane < k) {
         const bool ok = seq != INT64_MAX;
-        out_idx[q * k + lane] = ok ? seq * seq_mul + seq_add : -1;
-        out_score[q * k + lane] = ok ? (float)sc : -INFINITY;
-        if (out_score64) out_score64[q * k + lane] = ok ? sc : -INFINITY;
+        a.out_idx[q * k + lane] = ok ? seq * a.seq_mul + a.seq_add : -1;
+        a.out_score[q * k + lane] = ok ? (float)sc : -INFINITY;
+        if (a.out_score64) a.out_score64[q * k + lane] = ok ? sc : -INFINITY;
     }
-    if (peers) {                                           // row-sharded store: see finish_kernel step 4b
-        const int slot = (int)(step & 3);
+    if (a.peers) {                                              // row-sharded store: see finish_kernel step 4b
+        const int slot = (int)(a.step & 3);
         if (lane < k) {
             const bool ok = seq != INT64_MAX;
-            const int64_t iw = ok ? seq * seq_mul + seq_add : -1;
+            const int64_t iw = ok ? seq * a.seq_mul + a.seq_add : -1;
             const int64_t sw = __double_as_longlong(ok ? sc : -INFINITY);
-            for (int p = 0; p < world; ++p) {
-                int64_t* blk = reinterpret_cast<int64_t*>(peers[p] + ((int64_t)slot * world + rank) * block_bytes);
+            for (int pr = 0; pr < a.world; ++pr) {
+                int64_t* blk = reinterpret_cast<int64_t*>(a.peers[pr] + ((int64_t)slot * a.world + a.rank) * a.block_bytes);
                 blk[q * k + lane] = iw;
-                blk[nq * k + q * k + lane] = sw;
+                blk[a.nq * k + q * k + lane] = sw;
             }
         }
         __syncwarp();
         if (lane == 0) {
             __threadfence_system();
-            const uint32_t old = atomicAdd(done_counter, 1u);
-            if (old == (uint32_t)(nq - 1)) {
-                *done_counter = 0u;
+            const uint32_t old = atomicAdd(a.done_counter, 1u);
+            if (old == (uint32_t)(a.nq - 1)) {
+                *a.done_counter = 0u;
                 __threadfence_system();
-                for (int p = 0; p < world; ++p) {
-                    uint64_t* flag = reinterpret_cast<uint64_t*>(peers[p] + flags_off) + (int64_t)slot * world + rank;
-                    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(flag), "l"((uint64_t)(step + 1)) : "memory");
+                for (int pr = 0; pr < a.world; ++pr) {
+                    uint64_t* flag = reinterpret_cast<uint64_t*>(a.peers[pr] + a.flags_off) + (int64_t)slot * a.world + a.rank;
+                    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(flag), "l"((uint64_t)(a.step + 1)) : "memory");
                 }
             }
         }
@@ -507,31 +578,34 @@ rescore_kernel(const uint64_t* __restrict__ surv, const __nv_bfloat16* __restric
         bool bad = false;
         if (pool_full) {
             const double a_min = nqn > 0.0 ? (double)key_score(bound) / sqrt(nqn) : 0.0;
-            bad = !(a_min + err < e_k);
+            bad = !(a_min + a.err < e_k);
         }
-        if (flags) flags[q] = bad ? 1 : 0;
-        if (bad && inexact) atomicAdd(inexact, 1);
+        if (a.flags) a.flags[q] = bad ? 1 : 0;
+        if (bad && a.inexact) atomicAdd(a.inexact, 1);
     }
+}
+
+static size_t finish_sel_smem(int ld) { return (size_t)ld * 10 + SEL_ROWS * ((size_t)ld * 2 + 16); }
+
+template <int LL>
+static cudaError_t launch_finish_sel(const FinishArgs& a, cudaStream_t st) {
+    const size_t smem = finish_sel_smem(a.ld);
+    if (smem > 48 * 1024) {                                     // dims above 1024 only (the attribute is per device)
+        cudaError_t e = cudaFuncSetAttribute(finish_sel_kernel<LL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    finish_sel_kernel<LL><<<(unsigned)a.nq, FIN_WARPS * 32, smem, st>>>(a);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_finish(const FinishArgs& a, cudaStream_t st) {
     if (a.nq <= 0) return cudaSuccess;
-    const size_t row_bytes = (size_t)a.ld * 2 + 16;
-    if (a.surv && (RS_ROWS + 1) * row_bytes <= 100 * 1024) {
-        // split form: merge (warp per query) + re-score (CTA per query, 16 rows staged per round)
-        merge_lists_kernel<<<(unsigned)((a.nq + 3) / 4), 128, 0, st>>>(
-            a.partials, a.slots, a.list_len, a.pool_n, a.rows_per_group, a.lists_base, a.groups_rem, a.lists_extra, a.nq,
-            a.gthr, a.surv);
-        cudaError_t e = cudaGetLastError();
-        if (e != cudaSuccess) return e;
-        const size_t smem2 = (RS_ROWS + 1) * row_bytes;
-        e = cudaFuncSetAttribute(rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
-        if (e != cudaSuccess) return e;
-        rescore_kernel<<<(unsigned)a.nq, FIN_WARPS * 32, smem2, st>>>(
-            a.surv, (const __nv_bfloat16*)a.qb, (const __nv_bfloat16*)a.vec, a.ld, a.nq, a.capacity, a.head, a.base_seq,
-            a.seq_mul, a.seq_add, a.k, a.err, a.out_idx, a.out_score, a.out_score64, a.flags, a.inexact, a.peers, a.world,
-            a.rank, a.block_bytes, a.flags_off, a.step, a.done_counter);
-        return cudaGetLastError();
+    // default: selective re-score; rows too long for its shared-memory staging (dim > 4096), or an
+    // explicit request (option 9), take the original kernel
+    if (!a.legacy && finish_sel_smem(a.ld) <= 200 * 1024) {
+        if (a.list_len == 8) return launch_finish_sel<8>(a, st);
+        if (a.list_len == 16) return launch_finish_sel<16>(a, st);
+        return launch_finish_sel<32>(a, st);
     }
     // stage the surviving rows in shared memory when they fit (pool_n + 1 rows of ld*2+16 bytes)
     const size_t smem = (size_t)(a.pool_n + 1) * ((size_t)a.ld * 2 + 16);

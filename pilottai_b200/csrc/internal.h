@@ -58,7 +58,7 @@ cudaError_t launch_prepare(const float* q, int64_t nq, int dim, int ld, void* qb
 
 struct FinishArgs {
     const uint64_t* partials; int slots; int list_len;   // slots = allocated lists per query
-    int pool_n;                 // survivors re-scored exactly (32)
+    int pool_n;                 // survivors the merge keeps per query (32)
     const uint32_t* gthr;       // [nq] largest threshold any list of the query ended with (may be NULL)
     int rows_per_group, lists_base, groups_rem, lists_extra;  // lists of query q: lists_base + (q/rows_per_group < groups_rem ? lists_extra : 0)
     const void* qb; const void* vec; int ld;
@@ -73,7 +73,7 @@ struct FinishArgs {
     int world = 1, rank = 0;
     int64_t block_bytes = 0, flags_off = 0, step = 0;
     uint32_t* done_counter = nullptr;
-    uint64_t* surv = nullptr;   // [nq][33] scratch: set = use the split form (merge kernel + re-score kernel)
+    bool legacy = false;        // true: the original one-kernel form that re-scores all pool_n survivors
 };
 cudaError_t launch_finish(const FinishArgs& a, cudaStream_t st);
 

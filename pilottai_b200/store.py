@@ -68,11 +68,9 @@ class SemanticStore:
     def set_list_len(self, n: int) -> None:
         check(self._lib.pilott_mem_set_option(self._h, 3, int(n)))
 
-    def set_finish_form(self, split: int) -> None:
-        check(self._lib.pilott_mem_set_option(self._h, 9, int(split)))
-
-    def set_pool(self, n: int) -> None:
-        check(self._lib.pilott_mem_set_option(self._h, 8, int(n)))
+    def set_finish_form(self, form: int) -> None:
+        """0: selective re-score (default); 1: the original kernel that re-scores all 32 survivors."""
+        check(self._lib.pilott_mem_set_option(self._h, 9, int(form)))
 
     def set_profile(self, on: bool) -> None:
         check(self._lib.pilott_mem_set_option(self._h, 4, 1 if on else 0))
@@ -88,6 +86,8 @@ class SemanticStore:
         check(self._lib.pilott_mem_set_option(self._h, 6, int(offset)))
 
     def set_debug(self, flags: int) -> None:
+        """Developer switches of the scan kernel: only in a -DPILOTT_DEBUG build (PILOTT_DEBUG=1
+        python -m pilottai_b200.build --force); the production library refuses anything but 0."""
         check(self._lib.pilott_mem_set_option(self._h, 2, int(flags)))
 
     def launch_count(self) -> int:
@@ -295,7 +295,7 @@ class SemanticStore:
         [nq, k], query_ids an int32 CUDA tensor or None.  Scratch is the library's fixed
         16 MiB device array, so nq * row_stride * 2 + n_selected * rows_held * 8 bytes must
         fit in it (PilottError otherwise); calls that overlap on the GPU share that array and
-        race.  The first call on a device should precede any stream capture."""
+        race.  Its one-time set-up per device runs when a store is created, not in this call."""
         idx, sc, sc64 = out
         nsel = q.shape[0] if query_ids is None else query_ids.numel()
         check(self._lib.pilott_mem_search_exact_noalloc(

@@ -274,9 +274,10 @@ def test_wide_vectors_unstaged_rescore(torch_cuda, kernel):
     gs.close()
 
 
-def test_split_finish_form_gives_the_same_answers(torch_cuda):
-    """Option 9: the finish step as two kernels (merge per warp, re-score with 16 rows staged per
-    round and one partial sum per lane) -- same indices, same fp64 scores, same flags."""
+def test_both_finish_forms_give_the_same_answers(torch_cuda):
+    """Option 9: the default finish step re-scores only the survivors that can reach the top-k (and
+    lets the gap check prove the cut); form 1 is the original kernel that re-scores all 32 -- same
+    indices, same fp64 scores, both against the oracle."""
     gs, os_, x = _fill(9000, 768, 8192, seed=21)          # ring wrapped once
     q = synth.queries(300, 768, seed=22)
     for form in (1, 0, 1):

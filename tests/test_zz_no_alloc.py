@@ -9,7 +9,8 @@ device image and offers this entry point, which only launches kernels.
 Checked here, through the C ABI: two calls in a row (the second with other queries, so stale
 scratch from the first would show) each return exactly what the allocating entry point
 pilott_mem_search_exact returns -- indices equal, fp64 scores bit-identical, the same bar as
-tests/test_gpu_retrieval.py -- and an over-sized request is refused with a clear message.
+tests/test_gpu_retrieval.py -- without the device's free memory moving (the array is loaded
+when the store is created, not by the call), and over-sized requests are refused with a clear message.
 Collected last (file name) so a `-x` run has already been through every other test.
 """
 import numpy as np
@@ -48,8 +49,12 @@ def test_noalloc_matches_allocating_entry_point_twice_in_a_row(torch_cuda):
         q = torch.from_numpy(synth.queries(nq, dim, seed=seed)).cuda()
         qids = None if ids is None else torch.tensor(ids, dtype=torch.int32, device="cuda")
         want = st.search_exact(q, k, query_ids=qids, out=_outs(torch, nq, k), **flt)
-        got = st.search_exact_noalloc(q, k, _outs(torch, nq, k), query_ids=qids, **flt)
+        bufs = _outs(torch, nq, k)
         torch.cuda.synchronize()
+        free_before = torch.cuda.mem_get_info(0)[0]           # cudaMemGetInfo: the driver's own count
+        got = st.search_exact_noalloc(q, k, bufs, query_ids=qids, **flt)
+        torch.cuda.synchronize()
+        assert torch.cuda.mem_get_info(0)[0] == free_before, f"call {call} changed the device's free memory"
         for w, g, name in zip(want, got, ("index", "score", "score64")):
             assert torch.equal(w, g), f"call {call}: {name} differs from pilott_mem_search_exact"
         rows = list(range(nq)) if ids is None else ids
@@ -69,6 +74,10 @@ def test_noalloc_rejects_requests_beyond_the_fixed_scratch(torch_cuda):
         st.search_exact_noalloc(q, 5, _outs(torch, nq, 5))
     assert ei.value.code == _lib.EINVAL
     assert str(_lib.NOALLOC_SCRATCH_BYTES) in str(ei.value) and "scratch" in str(ei.value)
+    many = torch.zeros(65536, dtype=torch.int32, device="cuda")  # more selected queries than one launch grid takes
+    with pytest.raises(_lib.PilottError) as ei:
+        st.search_exact_noalloc(q, 5, _outs(torch, nq, 5), query_ids=many)
+    assert ei.value.code == _lib.EINVAL and "65535" in str(ei.value)
     ok = torch.arange(8, dtype=torch.int32, device="cuda")      # a subset that fits is served
     got = st.search_exact_noalloc(q, 5, _outs(torch, nq, 5), query_ids=ok)
     want = st.search_exact(q, 5, query_ids=ok, out=_outs(torch, nq, 5))

@@ -15,8 +15,7 @@ torch.cuda.init()
 dev = torch.device("cuda:0")
 g = torch.Generator(device=dev); g.manual_seed(1234)
 st = SemanticStore(dim, n, 0)
-st.set_pool(int(os.environ.get("QB_POOL", "0")))
-st.set_finish_form(int(os.environ.get("QB_SPLIT", "0")))
+st.set_finish_form(int(os.environ.get("QB_FINISH", "0")))
 t0 = time.time()
 for lo in range(0, n, 131072):
     m = min(131072, n - lo)
@@ -40,7 +39,8 @@ for kern in kernels:
         if ":" in kern:
             kern, dbg = kern.split(":"); dbg = int(dbg)
         st.set_list_len(ll)
-        st.set_debug(dbg)
+        if dbg:
+            st.set_debug(dbg)
         st.set_kernel(kern)
         for _ in range(2):
             st.search_into(q, k, idx, sc, sc64, inex, flags)
@@ -60,7 +60,8 @@ for kern in kernels:
         print(f"{kern}: FAILED {ex}", flush=True)
         break
 # append throughput (K1)
-xb = torch.randn(131072, dim, generator=g, device=dev)
+nb = min(131072, n)
+xb = torch.randn(nb, dim, generator=g, device=dev)
 torch.cuda.synchronize()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record()
@@ -68,5 +69,5 @@ for _ in range(5):
     st.append(xb)
 e1.record(); torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / 5
-byts = 131072 * (4 * dim + 2 * st.info()["row_stride"] + 32)
-print(f"append  : {ms:8.3f} ms / 131072 rows  {131072/(ms*1e-3):12.0f} rows/s  {byts/(ms*1e-3)/1e9:7.1f} GB/s")
+byts = nb * (4 * dim + 2 * st.info()["row_stride"] + 32)
+print(f"append  : {ms:8.3f} ms / {nb} rows  {nb/(ms*1e-3):12.0f} rows/s  {byts/(ms*1e-3)/1e9:7.1f} GB/s")
