@@ -79,6 +79,12 @@ int pilott_mem_info(const pilott_mem_t* h, int64_t* total, int64_t* count, int64
 int pilott_mem_set_option(pilott_mem_t* h, int which, int64_t value);
 /* Kernel launches enqueued by this handle since creation (bench bookkeeping). */
 int64_t pilott_mem_launch_count(const pilott_mem_t* h);
+/* How many queries the gap check of the fused path flagged ("not provably exact") in all searches on
+ * this handle since creation or since the last call with reset != 0 -- unlike *out_inexact_dev,
+ * which every search zeroes, nothing is lost between batches, so a pipeline that keeps several
+ * searches in flight (and a row-sharded job, which sums it over ranks) can assert "no query went
+ * unproven" once at the end.  Synchronises the device.  No counterpart in the reference. */
+int pilott_mem_flagged_total(pilott_mem_t* h, int64_t* total, int reset);
 /* Waits for the recorded scan kernels, returns their summed device time and count since the
  * last read (option 4 must be on), and resets the window. */
 int pilott_mem_profile_read(pilott_mem_t* h, double* scan_ms_total, int64_t* n_scans);

@@ -29,6 +29,7 @@ def lib():
         _lib = C.CDLL(_SO)
         _lib.oracle_exact_scores.restype = None
         _lib.oracle_search.restype = None
+        _lib.oracle_search_rows.restype = None
     return _lib
 
 
@@ -70,4 +71,47 @@ def search(store: OracleStore, queries, k, min_priority=0, req_tagmask=0, now_us
         from concurrent.futures import ThreadPoolExecutor
         with ThreadPoolExecutor(nthr) as ex:
             list(ex.map(lambda i: run(bounds[i], bounds[i + 1]), range(nthr)))
+    return out_idx, out_sc
+
+
+def search_rows(store, queries, k, min_priority=0, req_tagmask=0, now_us=0, threads=None, q_bits=None):
+    """Same answers as search(), organised for long corpora: the slot range is split across host
+    threads, each thread scores ALL queries against its rows in one pass (oracle_search_rows), and
+    the per-range top-k lists are merged by (score desc, sequence asc).  `store` needs the
+    OracleStore attributes (vec [capacity, dim] uint16, prio, tagmask, expires_us, capacity, dim,
+    slot_seq()); q_bits passes queries that are already bf16 bit patterns."""
+    if q_bits is None:
+        q_bits = bf16_round_bits(np.atleast_2d(np.asarray(queries, np.float32)))
+    q_bits = np.ascontiguousarray(q_bits, np.uint16)
+    Q, D = q_bits.shape
+    seq = np.ascontiguousarray(store.slot_seq(), np.int64)
+    N = int(store.capacity)
+    nthr = max(1, min(threads or (os.cpu_count() or 1), max(1, N // 1024)))
+    bounds = np.linspace(0, N, nthr + 1).astype(np.int64)
+    part_idx = np.empty((nthr, Q, k), np.int64)
+    part_sc = np.empty((nthr, Q, k), np.float64)
+    L = lib()
+
+    def run(t):
+        L.oracle_search_rows(_p(q_bits), C.c_int64(Q), _p(store.vec), C.c_int64(int(bounds[t])),
+                             C.c_int64(int(bounds[t + 1])), C.c_int(D), C.c_int64(D),
+                             C.c_int64(store.vec.shape[1]), _p(seq), _p(store.prio), _p(store.tagmask),
+                             _p(store.expires_us), C.c_int32(min_priority), C.c_uint64(req_tagmask),
+                             C.c_int64(now_us), C.c_int(k), _p(part_idx[t]), _p(part_sc[t]))
+
+    if nthr == 1:
+        run(0)
+    else:
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(nthr) as ex:
+            list(ex.map(run, range(nthr)))
+    out_idx = np.full((Q, k), -1, np.int64)
+    out_sc = np.full((Q, k), -np.inf, np.float64)
+    for qi in range(Q):
+        ci, cs = part_idx[:, qi].ravel(), part_sc[:, qi].ravel()
+        ok = ci >= 0
+        ci, cs = ci[ok], cs[ok]
+        order = np.lexsort((ci, -cs))[:k]
+        out_idx[qi, :order.size] = ci[order]
+        out_sc[qi, :order.size] = cs[order]
     return out_idx, out_sc

@@ -87,3 +87,69 @@ void oracle_search(const uint16_t* q, int64_t Q, const uint16_t* m, int64_t N, i
     }
     free(sc);
 }
+
+/* ---- the same search, organised for long corpora (bench.py's parity sample over 1 M - 10 M rows):
+ * one pass over a RANGE of rows scores all Q queries against each row, so a row is converted to
+ * fp64 and its norm summed once instead of once per query, and callers split the corpus into row
+ * ranges across host threads and merge the per-range lists (oracle/retrieval_c.py).  Arithmetic and
+ * order are exactly those of oracle_exact_scores / oracle_search above -- eight interleaved partial
+ * sums per quantity, the fixed combining tree, den = sqrt(nq)*sqrt(nm), (score desc, seq asc) --
+ * and tests/test_oracle_twin.py holds this function to them and to the numpy statement bit for bit.
+ * The inner loops are written eight lanes wide so that the compiler can keep one partial sum per
+ * vector lane; target_clones picks the widest vector unit of the host at load time (the result
+ * does not depend on it: every lane performs the same IEEE operations in the same order). */
+#if defined(__x86_64__) && defined(__GNUC__)
+#define ORACLE_CLONES __attribute__((target_clones("avx512f", "avx2", "default")))
+#else
+#define ORACLE_CLONES
+#endif
+
+ORACLE_CLONES
+void oracle_search_rows(const uint16_t* q, int64_t Q, const uint16_t* m, int64_t n_lo, int64_t n_hi,
+                        int D, int64_t ld_q, int64_t ld_m, const int64_t* seq, const int32_t* prio,
+                        const uint64_t* tagmask, const int64_t* expires_us, int32_t min_prio,
+                        uint64_t req_tags, int64_t now_us, int k, int64_t* out_idx, double* out_score) {
+    const int D8 = (D + 7) & ~7;                       /* padded with zeros: they add exactly nothing */
+    double* qd = (double*)calloc((size_t)Q * D8, sizeof(double));
+    double* sq = (double*)malloc(sizeof(double) * (size_t)Q);
+    double* vd = (double*)calloc((size_t)D8, sizeof(double));
+    int* have = (int*)calloc((size_t)Q, sizeof(int));
+    for (int64_t qi = 0; qi < Q; ++qi) {
+        double pq[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int d = 0; d < D; ++d) qd[qi * D8 + d] = bf2d(q[qi * ld_q + d]);
+        for (int d = 0; d < D8; d += 8)
+            for (int j = 0; j < 8; ++j) pq[j] += qd[qi * D8 + d + j] * qd[qi * D8 + d + j];
+        sq[qi] = sqrt(tree8(pq));
+        for (int j = 0; j < k; ++j) { out_idx[qi * k + j] = -1; out_score[qi * k + j] = -INFINITY; }
+    }
+    for (int64_t n = n_lo; n < n_hi; ++n) {
+        if (seq[n] < 0) continue;
+        if (prio[n] < min_prio) continue;
+        if ((tagmask[n] & req_tags) != req_tags) continue;
+        if (expires_us[n] != 0 && now_us > expires_us[n]) continue;
+        const uint16_t* row = m + n * ld_m;
+        double pm[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int d = 0; d < D; ++d) vd[d] = bf2d(row[d]);
+        for (int d = 0; d < D8; d += 8)
+            for (int j = 0; j < 8; ++j) pm[j] += vd[d + j] * vd[d + j];
+        const double sm = sqrt(tree8(pm));
+        for (int64_t qi = 0; qi < Q; ++qi) {
+            const double* qq = qd + qi * D8;
+            double pd[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+            for (int d = 0; d < D8; d += 8)
+                for (int j = 0; j < 8; ++j) pd[j] += qq[d + j] * vd[d + j];
+            const double den = sq[qi] * sm;
+            const double s = den > 0.0 ? tree8(pd) / den : 0.0;
+            int64_t* bi = out_idx + qi * k;
+            double* bs = out_score + qi * k;
+            if (have[qi] == k && !before(s, seq[n], bs[k - 1], bi[k - 1])) continue;
+            int j = have[qi] < k ? have[qi] : k - 1;
+            while (j > 0 && before(s, seq[n], bs[j - 1], bi[j - 1])) {
+                bs[j] = bs[j - 1]; bi[j] = bi[j - 1]; --j;
+            }
+            bs[j] = s; bi[j] = seq[n];
+            if (have[qi] < k) ++have[qi];
+        }
+    }
+    free(qd); free(sq); free(vd); free(have);
+}

@@ -30,6 +30,7 @@ SIGNATURES = {
                                   C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "pilott_mem_set_option": (C.c_int, [c_vp, C.c_int, c_i64]),
     "pilott_mem_launch_count": (c_i64, [c_vp]),
+    "pilott_mem_flagged_total": (C.c_int, [c_vp, C.POINTER(c_i64), C.c_int]),
     "pilott_mem_profile_read": (C.c_int, [c_vp, C.POINTER(C.c_double), C.POINTER(c_i64)]),
     "pilott_mem_append": (C.c_int, [c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, C.POINTER(c_i64), c_vp]),
     "pilott_mem_append_host": (C.c_int, [c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, C.POINTER(c_i64)]),

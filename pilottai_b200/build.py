@@ -12,6 +12,9 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libpilott_b200.so")
+# host-side helper (CPython extension, plain C): task dicts -> routing kernel columns
+TASKENC_SRC = os.path.join(CSRC, "task_encode.c")
+TASKENC_OUT = os.path.join(HERE, "_taskenc" + (__import__("sysconfig").get_config_var("EXT_SUFFIX") or ".so"))
 SOURCES = ["abi.cu", "store_kernels.cu", "scan_generic.cu", "scan_tc.cu", "finish.cu", "route.cu", "xchg.cu"]
 HEADERS = ["common.cuh", "internal.h", os.path.join("..", "..", "include", "pilott_b200.h")]
 NVCC_FLAGS = [
@@ -35,7 +38,18 @@ def needs_build() -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
+def build_taskenc(force: bool = False) -> str:
+    import sysconfig
+    if not force and os.path.exists(TASKENC_OUT) and os.path.getmtime(TASKENC_OUT) >= os.path.getmtime(TASKENC_SRC):
+        return TASKENC_OUT
+    cmd = [os.environ.get("CC", "gcc"), "-O2", "-fPIC", "-shared", "-Wall", "-I", sysconfig.get_paths()["include"],
+           TASKENC_SRC, "-o", TASKENC_OUT]
+    subprocess.check_call(cmd)
+    return TASKENC_OUT
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
+    build_taskenc(force)
     if not force and not needs_build():
         return OUT
     objs = []

@@ -142,6 +142,7 @@ struct pilott_mem {
     int64_t* expires = nullptr;
     float* scale = nullptr;
     float* tile_max = nullptr;
+    unsigned long long* flagged_dev = nullptr;   // queries flagged by the gap check since the last pilott_mem_flagged_total(reset)
     DevBuf qbuf, partials, gthr, exact_scratch, stage_dev, result_dev, misc_dev, refine, result_ids, largek;
     HostBuf stage_host;
     cudaStream_t own_stream = nullptr;
@@ -352,6 +353,7 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
         f.peers = x->peers_dev; f.world = x->world; f.rank = x->rank; f.block_bytes = x->block_bytes;
         f.flags_off = x->flags_off; f.step = step; f.done_counter = x->done_dev;
     }
+    f.flagged_total = h->flagged_dev;
     f.legacy = h->opt_finish == 1;
     CK(pilott::launch_finish(f, st));
     h->launches += 2;
@@ -655,6 +657,11 @@ int pilott_mem_create(int dim, int64_t capacity, int device, pilott_mem_t** out)
         if (e != cudaSuccess) rc = fail_cuda(e, "cudaStreamCreate");
     }
     if (rc == PILOTT_OK) {
+        cudaError_t e = cudaMalloc(&h->flagged_dev, 8);
+        if (e == cudaSuccess) e = cudaMemset(h->flagged_dev, 0, 8);
+        if (e != cudaSuccess) rc = fail_cuda(e, "cudaMalloc(flagged counter)");
+    }
+    if (rc == PILOTT_OK) {
         cudaError_t e = cudaEventCreateWithFlags(&h->ev_dev, cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_own, cudaEventDisableTiming);
         if (e != cudaSuccess) rc = fail_cuda(e, "cudaEventCreate");
@@ -673,6 +680,7 @@ int pilott_mem_create(int dim, int64_t capacity, int device, pilott_mem_t** out)
     }
     if (rc != PILOTT_OK) {
         free_columns(h);
+        cudaFree(h->flagged_dev);
         if (h->own_stream) cudaStreamDestroy(h->own_stream);
         if (h->ev_dev) cudaEventDestroy(h->ev_dev);
         if (h->ev_own) cudaEventDestroy(h->ev_own);
@@ -690,6 +698,7 @@ int pilott_mem_destroy(pilott_mem_t* h) {
     DeviceGuard g(h->device);
     cudaDeviceSynchronize();
     free_columns(h);
+    cudaFree(h->flagged_dev);
     h->qbuf.release(); h->partials.release(); h->gthr.release(); h->exact_scratch.release(); h->stage_dev.release();
     h->result_dev.release(); h->misc_dev.release(); h->refine.release(); h->result_ids.release(); h->largek.release();
     h->stage_host.release();
@@ -769,6 +778,17 @@ int pilott_mem_set_option(pilott_mem_t* h, int which, int64_t value) {
 }
 
 int64_t pilott_mem_launch_count(const pilott_mem_t* h) { return h ? h->launches : 0; }
+
+int pilott_mem_flagged_total(pilott_mem_t* h, int64_t* total, int reset) {
+    if (!h) return fail(PILOTT_EINVAL, "handle is NULL");
+    DeviceGuard g(h->device);
+    CK(cudaDeviceSynchronize());
+    unsigned long long v = 0;
+    CK(cudaMemcpy(&v, h->flagged_dev, 8, cudaMemcpyDeviceToHost));
+    if (reset) CK(cudaMemset(h->flagged_dev, 0, 8));
+    if (total) *total = (int64_t)v;
+    return PILOTT_OK;
+}
 
 int pilott_mem_profile_read(pilott_mem_t* h, double* scan_ms_total, int64_t* n_scans) {
     if (!h) return fail(PILOTT_EINVAL, "handle is NULL");

@@ -135,7 +135,8 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_l
               float* __restrict__ out_score, double* __restrict__ out_score64,
               uint8_t* __restrict__ flags, int32_t* __restrict__ inexact, int stage_rows,
               const uint32_t* __restrict__ gthr, unsigned char* const* __restrict__ peers, int world, int rank,
-              int64_t block_bytes, int64_t flags_off, int64_t step, uint32_t* __restrict__ done_counter) {
+              int64_t block_bytes, int64_t flags_off, int64_t step, uint32_t* __restrict__ done_counter,
+              unsigned long long* __restrict__ flagged_total) {
     extern __shared__ __align__(16) unsigned char s_rows[];     // [pool_n + 1][ld*2 + 16] when stage_rows
     __shared__ uint64_t s_pool[FIN_WARPS][32];
     __shared__ double s_part[3][FIN_WARPS][32];              // per-warp pair sums of (dot, nq, nm) per candidate
@@ -332,6 +333,7 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_l
         }
         if (flags) flags[q] = bad ? 1 : 0;
         if (bad && inexact) atomicAdd(inexact, 1);
+        if (bad && flagged_total) atomicAdd(flagged_total, 1ull);
     }
 }
 
@@ -582,6 +584,7 @@ finish_sel_kernel(const __grid_constant__ FinishArgs a) {
         }
         if (a.flags) a.flags[q] = bad ? 1 : 0;
         if (bad && a.inexact) atomicAdd(a.inexact, 1);
+        if (bad && a.flagged_total) atomicAdd(a.flagged_total, 1ull);
     }
 }
 
@@ -619,7 +622,7 @@ cudaError_t launch_finish(const FinishArgs& a, cudaStream_t st) {
         (const __nv_bfloat16*)a.qb, (const __nv_bfloat16*)a.vec, a.ld, a.nq,
         a.capacity, a.head, a.base_seq, a.seq_mul, a.seq_add, a.k, a.err, a.out_idx, a.out_score, a.out_score64,
         a.flags, a.inexact, stage_rows, a.gthr, a.peers, a.world, a.rank, a.block_bytes, a.flags_off, a.step,
-        a.done_counter);
+        a.done_counter, a.flagged_total);
     return cudaGetLastError();
 }
 

@@ -73,6 +73,7 @@ struct FinishArgs {
     int world = 1, rank = 0;
     int64_t block_bytes = 0, flags_off = 0, step = 0;
     uint32_t* done_counter = nullptr;
+    unsigned long long* flagged_total = nullptr;   // handle-lifetime count of flagged queries (never zeroed by a search)
     bool legacy = false;        // true: the original one-kernel form that re-scores all pool_n survivors
 };
 cudaError_t launch_finish(const FinishArgs& a, cudaStream_t st);

@@ -186,6 +186,34 @@ def encode_tasks(tasks: Sequence[dict], vocab: Vocab) -> Dict[str, np.ndarray]:
     return {"req": req, "tags": tags, "type": typ, "flags": flags}
 
 
+try:                                   # C-speed encoder (pilottai_b200/csrc/task_encode.c, built by pilottai_b200.build)
+    from . import _taskenc
+except ImportError:                    # not built: the Python definition above does the same, ~50x slower
+    _taskenc = None
+
+
+def encode_task_batch(tasks: Sequence[dict], vocab: Vocab) -> Dict[str, np.ndarray]:
+    """encode_tasks plus the three get_task_priority inputs, through the C extension when it is there.
+    Keys: req, tags, type, flags (what pilott_route_score takes) and urgent, cx, ndeps (what
+    pilott_task_priority takes; cx is the complexity class 9 / 6 / 0 for > 8 / > 5 / else, so a
+    fractional complexity compares exactly like the reference's float does, router.py:139-142)."""
+    n, w = len(tasks), vocab.words
+    if _taskenc is not None and isinstance(tasks, list):
+        out = {"req": np.zeros((n, w), np.uint64), "tags": np.zeros((n, w), np.uint64), "type": np.empty(n, np.int32),
+               "flags": np.empty(n, np.uint8), "urgent": np.empty(n, np.uint8), "cx": np.empty(n, np.int32),
+               "ndeps": np.empty(n, np.int32)}
+        done = _taskenc.encode(tasks, vocab.cap, vocab.spec, w, out["req"], out["tags"], out["type"], out["flags"],
+                               out["urgent"], out["cx"], out["ndeps"])
+        if done == n:
+            return out
+    out = encode_tasks(tasks, vocab)               # a task the fast path declines: the definition handles the batch
+    cxs = [t.get("complexity", 1) for t in tasks]
+    out["urgent"] = np.array([1 if t.get("urgent", False) else 0 for t in tasks], np.uint8)
+    out["cx"] = np.array([9 if c > 8 else 6 if c > 5 else 0 for c in cxs], np.int32)
+    out["ndeps"] = np.array([len(t.get("dependencies", [])) for t in tasks], np.int32)
+    return out
+
+
 # ---- the engine ------------------------------------------------------------------------------------
 class RoutingEngine:
     """Device-resident agent table + one-call batched scoring/assignment."""
@@ -264,11 +292,22 @@ class RoutingEngine:
             out_a = torch.where(out_a >= 0, d_keep[out_a.clamp(min=0).long()], out_a)
         return out_a, out_s
 
-    def route(self, tasks: Sequence[dict], mode: str = "router", **cfg):
-        """Dict tasks -> (agent index list, score list) on the host."""
+    def encode(self, tasks: Sequence[dict]) -> Dict[str, np.ndarray]:
+        """Task dicts -> host columns (C extension when built; see encode_task_batch)."""
+        return encode_task_batch(tasks, self.vocab)
+
+    def to_device(self, arr: np.ndarray):
+        return self._d(arr)
+
+    def route(self, tasks: Sequence[dict], mode: str = "router", as_numpy: bool = False, **cfg):
+        """Dict tasks -> (agent index, score) per task on the host: lists, or numpy arrays
+        (int32 / fp64) with as_numpy=True -- the form a million-task batch wants."""
         if not tasks:
-            return [], []
-        a, s = self.route_encoded(encode_tasks(tasks, self.vocab), mode, **cfg)
+            return (np.empty(0, np.int32), np.empty(0, np.float64)) if as_numpy else ([], [])
+        enc = self.encode(tasks)
+        a, s = self.route_encoded({k: enc[k] for k in ("req", "tags", "type", "flags")}, mode, **cfg)
+        if as_numpy:
+            return a.cpu().numpy(), s.cpu().numpy()
         return a.cpu().tolist(), s.cpu().tolist()
 
     def priorities(self, tasks: Sequence[dict]) -> List[int]:
@@ -276,9 +315,8 @@ class RoutingEngine:
         torch = self._torch
         if not tasks:
             return []
-        urgent = torch.tensor([1 if t.get("urgent", False) else 0 for t in tasks], dtype=torch.uint8, device=self.device)
-        cx = torch.tensor([int(t.get("complexity", 1)) for t in tasks], dtype=torch.int32, device=self.device)
-        nd = torch.tensor([len(t.get("dependencies", [])) for t in tasks], dtype=torch.int32, device=self.device)
+        enc = self.encode(tasks)
+        urgent, cx, nd = self._d(enc["urgent"]), self._d(enc["cx"]), self._d(enc["ndeps"])
         out = torch.empty(len(tasks), dtype=torch.uint8, device=self.device)
         st = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
         check(self._lib.pilott_task_priority(ptr(urgent), ptr(cx), ptr(nd), len(tasks), ptr(out), st))

@@ -55,7 +55,11 @@ class ShardedSemanticStore:
         self.exchange = exchange if world > 1 else "none"
         self._xchg = {}                                 # (nq, k) -> [handle, next step]
         self._ridx = {}                                 # cached row-selection indices for device appends
-        self.local = SemanticStore(dim, (capacity + world - 1) // world, device)
+        if capacity % world:
+            # with a remainder the shards together would hold more rows than one ring of `capacity`,
+            # and a search could return rows a single store had already evicted
+            raise ValueError(f"capacity ({capacity}) must be a multiple of the number of shards ({world})")
+        self.local = SemanticStore(dim, capacity // world, device)
         self.local.set_sequence_map(world, rank)
         self.dim, self.device = dim, device
         self.total = 0                                  # global rows ever appended
@@ -132,7 +136,10 @@ class ShardedSemanticStore:
         buffer slots a caller overlaps the exchange of batch i with the local search of batch i+1
         (at most ONE search_begin ahead of the matching search_end: the exchange has 4 slots).
         resolve=True reads the local inexact counter (one host sync) and repairs flagged queries
-        before the exchange; with resolve=False the caller checks the counter search_end() returns."""
+        before the exchange.  With resolve=False flagged rows are exchanged as they are, and every
+        rank only sees its OWN counter: sum `self.local.flagged_total()` over the ranks (one
+        all-reduce, at any later point -- the library counts across searches) before trusting the
+        merged results, as bench.py does."""
         b = self._buffers(q.shape[0], k, q.device, slot)
         xs = self._exchange_for(q.shape[0], k) if self.exchange == "p2p" else None
         large = k > _lib.MAX_FUSED_K                      # local top-k through the threshold-collect path (exact, synchronous)

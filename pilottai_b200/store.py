@@ -93,6 +93,13 @@ class SemanticStore:
     def launch_count(self) -> int:
         return int(self._lib.pilott_mem_launch_count(self._h))
 
+    def flagged_total(self, reset: bool = False) -> int:
+        """Queries the fused path flagged as not provably exact since creation / the last reset
+        (pilott_mem_flagged_total; synchronises the device)."""
+        n = C.c_int64()
+        check(self._lib.pilott_mem_flagged_total(self._h, C.byref(n), 1 if reset else 0))
+        return n.value
+
     def clear(self) -> None:
         check(self._lib.pilott_mem_clear(self._h, None))
 

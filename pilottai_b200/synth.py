@@ -115,3 +115,45 @@ def task_table(n_tasks: int, seed: int = 43) -> List[Dict]:
         t["priority"] = int(rng.integers(0, 4))
         tasks.append(t)
     return tasks
+
+
+def task_table_fast(n_tasks: int, seed: int = 43) -> List[Dict]:
+    """Same distribution as task_table, drawn column-wise (a million dicts in seconds instead of a
+    minute; a different random stream, so the two tables differ row by row)."""
+    rng = np.random.default_rng(seed)
+    caps, specs = np.array(CAP_VOCAB, dtype=object), np.array(SPEC_VOCAB, dtype=object)
+    has_req = rng.random(n_tasks) < 0.85
+    nreq = rng.integers(0, 4, n_tasks)
+    req_pick = np.argsort(rng.random((n_tasks, len(CAP_VOCAB))), axis=1)[:, :3] if n_tasks else np.zeros((0, 3), np.int64)
+    has_type = rng.random(n_tasks) < 0.9
+    known = rng.random(n_tasks) < 0.95
+    type_pick = rng.integers(0, len(SPEC_VOCAB), n_tasks)
+    ntag = rng.integers(0, 5, n_tasks)
+    tag_pick = np.argsort(rng.random((n_tasks, len(SPEC_VOCAB))), axis=1)[:, :4] if n_tasks else np.zeros((0, 4), np.int64)
+    empty_tags = rng.random(n_tasks) < 0.5
+    odd_tag = rng.random(n_tasks) < 0.05
+    cx = rng.integers(1, 11, n_tasks)
+    ndep = rng.integers(0, 8, n_tasks)
+    urgent = rng.random(n_tasks) < 0.1
+    prio = rng.integers(0, 4, n_tasks)
+    deps = [[f"d{j}" for j in range(m)] for m in range(8)]
+    cap_l, spec_l = caps.tolist(), specs.tolist()
+    tasks = []
+    for i in range(n_tasks):
+        t: Dict = {"id": f"task{i:07d}"}
+        if has_req[i]:
+            t["required_capabilities"] = [cap_l[c] for c in req_pick[i, :nreq[i]]]
+        if has_type[i]:
+            t["type"] = spec_l[type_pick[i]] if known[i] else "unknown_type"
+        if ntag[i] or empty_tags[i]:
+            tg = [spec_l[c] for c in tag_pick[i, :ntag[i]]]
+            if odd_tag[i]:
+                tg.append("not_in_vocab")
+            t["tags"] = tg
+        t["complexity"] = int(cx[i])
+        t["dependencies"] = deps[ndep[i]]
+        if urgent[i]:
+            t["urgent"] = True
+        t["priority"] = int(prio[i])
+        tasks.append(t)
+    return tasks
