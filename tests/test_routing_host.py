@@ -139,3 +139,35 @@ def test_task_delegator_bookkeeping_matches_the_reference_log(golden_dir):
     assert len(got) == len(want)
     for g, w in zip(got, want):
         assert g == w, (g, w)
+
+
+def test_c_task_encoder_equals_the_python_definition():
+    """pilottai_b200._taskenc (csrc/task_encode.c) against routing.encode_tasks, the definition:
+    every column equal on a seeded table with unknown capabilities / types / tags, tuples and sets
+    as containers, missing keys, fractional complexity; a task the fast path declines (a str where
+    a list belongs) sends the whole batch through the definition."""
+    import numpy as np
+    from pilottai_b200 import routing, synth
+    if routing._taskenc is None:
+        import pytest
+        pytest.skip("extension not built (python -m pilottai_b200.build)")
+    agents = synth.agent_table(300, seed=7)                      # > 64 capabilities? no: 64 + 64 names, 1 word
+    vocab = routing.Vocab(agents)
+    tasks = synth.task_table(500, seed=8) + synth.task_table_fast(500, seed=9)
+    tasks[3]["required_capabilities"] = tuple(tasks[3].get("required_capabilities", ["cap01"]))
+    tasks[4]["tags"] = {"spec01", "spec07", "nope"}
+    tasks[5]["complexity"] = 8.5
+    tasks[6].pop("complexity", None)
+    tasks[7]["required_capabilities"] = []
+    fast = routing.encode_task_batch(tasks, vocab)
+    slow = routing.encode_tasks(tasks, vocab)
+    for k in slow:
+        assert np.array_equal(fast[k], slow[k]), k
+    assert [routing.task_priority_host(t) for t in tasks] == [
+        3 if u else 2 if (c > 8 or d > 5) else 1 if (c > 5 or d > 3) else 0
+        for u, c, d in zip(fast["urgent"], fast["cx"], fast["ndeps"])]
+    odd = tasks[:10] + [{"required_capabilities": "cap01"}]      # a str iterates as characters in the reference
+    got = routing.encode_task_batch(odd, vocab)
+    want = routing.encode_tasks(odd, vocab)
+    for k in want:
+        assert np.array_equal(got[k], want[k]), k
