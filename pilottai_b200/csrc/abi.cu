@@ -169,6 +169,13 @@ struct pilott_mem {
     size_t ev_used = 0;
     int64_t launches = 0;
     int64_t generation = 0; // bumped by everything that changes which rows are held (append, clear, compact)
+    // The scale / tile_max columns of the last search stay valid while no row changed and the filter
+    // is the same (and, if any row may carry an expiry, the same `now`): the pre-pass is skipped then.
+    bool expiry_possible = false;           // some append since the last clear passed an expires column with a non-zero (or unseen) entry
+    bool sk_valid = false;
+    int64_t sk_gen = -1, sk_now = 0;
+    int32_t sk_prio = 0;
+    uint64_t sk_req = 0;
 };
 
 // Exchange buffers of one rank of a row-sharded store (xchg.cu).
@@ -205,6 +212,16 @@ int order_host_call(pilott_mem* h) {
     if (h->dev_pending) CK(cudaStreamWaitEvent(h->own_stream, h->ev_dev, 0));
     h->dev_pending = false;          // own_stream is now ordered behind it, and so is everything enqueued there later
     return PILOTT_OK;
+}
+
+// true: scale / tile_max already hold exactly what a pre-pass with these filters would write.
+bool scale_is_current(const pilott_mem* h, int32_t min_prio, uint64_t req, int64_t now_us) {
+    return h->sk_valid && h->sk_gen == h->generation && h->sk_prio == min_prio && h->sk_req == req &&
+           h->sk_now == (h->expiry_possible ? now_us : 0);
+}
+void scale_note(pilott_mem* h, int32_t min_prio, uint64_t req, int64_t now_us) {
+    h->sk_valid = true; h->sk_gen = h->generation; h->sk_prio = min_prio; h->sk_req = req;
+    h->sk_now = h->expiry_possible ? now_us : 0;
 }
 
 void free_columns(pilott_mem* h) {
@@ -277,9 +294,11 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
     rc = h->gthr.ensure(n_words * 4);
     if (rc) return rc;
     // one launch: query conversion + scale pre-pass + zeroing of those words and of the inexact counter
+    const bool do_scale = !scale_is_current(h, min_prio, req, now_us);
     CK(pilott::launch_prepare(q_dev, nq, h->dim, h->ld, h->qbuf.p, h->inv_norm, h->prio, h->tagmask, h->expires,
                               h->count, h->capacity, h->cap_pad, min_prio, req, now_us, h->scale, h->tile_max,
-                              (uint32_t*)h->gthr.p, (int64_t)n_words, out_inexact, st));
+                              (uint32_t*)h->gthr.p, (int64_t)n_words, out_inexact, do_scale, st));
+    scale_note(h, min_prio, req, now_us);
     h->launches += 1;
 
     int kern = pick_kernel(h);
@@ -441,7 +460,8 @@ int refine_core(pilott_mem* h, const float* q_dev, int64_t nq, const int32_t* qi
     // query conversion + scale pre-pass for THESE filters (the scan reads h->scale / h->tile_max)
     CK(pilott::launch_prepare(q_dev, nq, h->dim, h->ld, h->qbuf.p, h->inv_norm, h->prio, h->tagmask, h->expires,
                               h->count, h->capacity, h->cap_pad, min_prio, req, now_us, h->scale, h->tile_max,
-                              nullptr, 0, nullptr, st));
+                              nullptr, 0, nullptr, !scale_is_current(h, min_prio, req, now_us), st));
+    scale_note(h, min_prio, req, now_us);
     const double err = h->ld * 2.4e-7 > 1e-4 ? h->ld * 2.4e-7 : 1e-4;       // same bound as the gap check
     CK(pilott::launch_refine_prepare(h->qbuf.p, qids, nsel, nsel_pad, h->ld, out_idx, out_score64, k, err, qb2,
                                      thr_bits, cnt, n_ovf, st));
@@ -722,6 +742,7 @@ int pilott_mem_clear(pilott_mem_t* h, void* stream) {
     if (!h) return fail(PILOTT_EINVAL, "handle is NULL");
     (void)stream;
     h->total = 0; h->count = 0; h->head = 0;
+    h->expiry_possible = false;
     ++h->generation;
     return PILOTT_OK;
 }
@@ -810,6 +831,7 @@ static int append_core(pilott_mem_t* h, const float* x_dev, int64_t n, const int
                        const uint64_t* tagmask_dev, const int64_t* expires_us_dev, int64_t* first_seq,
                        void* stream) {
     if (first_seq) *first_seq = h->total;
+    if (expires_us_dev) h->expiry_possible = true;      // device column: its values are not visible here
     int64_t first_slot = h->head + h->count;
     if (first_slot >= h->capacity) first_slot -= h->capacity;
     CK(pilott::launch_append(x_dev, n, h->dim, h->ld, h->vec, h->inv_norm, h->prio, h->tagmask, h->expires,
@@ -860,14 +882,18 @@ int pilott_mem_append_host(pilott_mem_t* h, const float* x_host, int64_t n, cons
     memcpy(hs, x_host, xb);
     if (prio_host) memcpy(hs + off_p, prio_host, pb);
     if (tagmask_host) memcpy(hs + off_t, tagmask_host, tb);
-    if (expires_us_host) memcpy(hs + off_e, expires_us_host, eb);
+    bool any_exp = false;              // an all-zero column ("never expires") is the same as no column
+    if (expires_us_host) {
+        for (int64_t i = 0; i < n && !any_exp; ++i) any_exp = expires_us_host[i] != 0;
+        if (any_exp) memcpy(hs + off_e, expires_us_host, eb);
+    }
     cudaStream_t st = h->own_stream;
     rc = order_host_call(h);
     if (rc) return rc;
     CK(cudaMemcpyAsync(ds, hs, tot, cudaMemcpyHostToDevice, st));
     rc = append_core(h, (const float*)ds, n, prio_host ? (const int32_t*)(ds + off_p) : nullptr,
                            tagmask_host ? (const uint64_t*)(ds + off_t) : nullptr,
-                           expires_us_host ? (const int64_t*)(ds + off_e) : nullptr, first_seq, st);
+                           any_exp ? (const int64_t*)(ds + off_e) : nullptr, first_seq, st);
     if (rc) return rc;
     CK(cudaStreamSynchronize(st));
     h->own_pending = false;

@@ -10,6 +10,17 @@ constexpr int KP = 32;    // candidates kept per (query, slot) by the approximat
 constexpr int CAP = 64;   // per-row append buffer (KP survivors + pending appends)
 constexpr unsigned FULL = 0xffffffffu;
 
+// ---- programmatic dependent launch ----------------------------------------------------------
+// The kernels of one search step (prepare -> scan -> finish [-> merge]) are launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization: each lets its successor start launching at
+// once (pdl_trigger) and waits for its predecessor to have completed, memory flushed, before it
+// touches anything the predecessor wrote or still reads (pdl_wait).  Launch latency and the
+// prologue of kernel i+1 then overlap the tail of kernel i.  Both instructions are no-ops in a
+// kernel launched without the attribute.  Every kernel launched with it MUST call pdl_wait in every
+// CTA before its first global access: completion is transitive only through the waits.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---- order-preserving float <-> uint32, and the 64-bit candidate key -------------------
 // key = ord(score) << 32 | (0xFFFFFFFF - age):  larger key == better candidate
 // (higher score first, then OLDER row first: the reference returns older items first

@@ -380,6 +380,8 @@ finish_sel_kernel(const __grid_constant__ FinishArgs a) {
     const __nv_bfloat16* qb = reinterpret_cast<const __nv_bfloat16*>(a.qb);
     const __nv_bfloat16* vec = reinterpret_cast<const __nv_bfloat16*>(a.vec);
     const int chunks = ld / 8;                                  // 16-byte pieces per row
+    pdl_trigger();                                              // next step's prepare kernel may start launching
+    pdl_wait();                                                 // the scan's lists are complete and visible
 
     // 0. the query row is on its way while the lists are merged
     for (int c = tid; c < chunks; c += FIN_WARPS * 32) cp_async16(q16 + 16 * c, qb + q * ld + 8 * c);
@@ -597,8 +599,7 @@ static cudaError_t launch_finish_sel(const FinishArgs& a, cudaStream_t st) {
         cudaError_t e = cudaFuncSetAttribute(finish_sel_kernel<LL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
-    finish_sel_kernel<LL><<<(unsigned)a.nq, FIN_WARPS * 32, smem, st>>>(a);
-    return cudaGetLastError();
+    return launch_pdl(finish_sel_kernel<LL>, dim3((unsigned)a.nq), dim3(FIN_WARPS * 32), smem, st, a);
 }
 
 cudaError_t launch_finish(const FinishArgs& a, cudaStream_t st) {
@@ -971,6 +972,8 @@ topk_merge_kernel(const int64_t* __restrict__ idx, const double* __restrict__ sc
     double* s_sc = reinterpret_cast<double*>(sm_raw);
     int64_t* s_idx = reinterpret_cast<int64_t*>(s_sc + total);
     const int64_t q = blockIdx.x;
+    pdl_trigger();
+    pdl_wait();
     for (int i = threadIdx.x; i < total; i += blockDim.x) {
         const int sh = i / k, j = i % k;
         s_sc[i] = sc[(int64_t)sh * shard_stride + q * k + j];
@@ -1002,9 +1005,8 @@ cudaError_t launch_topk_merge(const int64_t* idx, const double* sc, int shards, 
                               double* out_score64, cudaStream_t st) {
     if (nq <= 0) return cudaSuccess;
     const size_t smem = (size_t)shards * k * 16;
-    topk_merge_kernel<<<(unsigned)nq, 256, smem, st>>>(idx, sc, shards, nq, k, shard_stride, out_idx, out_score,
-                                                       out_score64);
-    return cudaGetLastError();
+    return launch_pdl(topk_merge_kernel, dim3((unsigned)nq), dim3(256), smem, st, idx, sc, shards, nq, k, shard_stride,
+                      out_idx, out_score, out_score64);
 }
 
 }  // namespace pilott

@@ -6,6 +6,18 @@
 
 namespace pilott {
 
+// Launch with programmatic stream serialization (see common.cuh: pdl_trigger / pdl_wait).
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 struct ScanArgs {
     const void* qb;          // bf16 [nq_pad, ld] converted queries
     const void* vec;         // bf16 [capacity, ld]
@@ -54,7 +66,7 @@ cudaError_t launch_prepare(const float* q, int64_t nq, int dim, int ld, void* qb
                            const int32_t* prio, const uint64_t* tagmask, const int64_t* expires, int64_t nslots,
                            int64_t capacity, int64_t cap_pad, int32_t min_prio, uint64_t req, int64_t now_us,
                            float* scale, float* tile_max, uint32_t* zero_words, int64_t n_zero_words,
-                           int32_t* inexact, cudaStream_t st);
+                           int32_t* inexact, bool do_scale, cudaStream_t st);
 
 struct FinishArgs {
     const uint64_t* partials; int slots; int list_len;   // slots = allocated lists per query

@@ -314,6 +314,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic stores -> visible to UMMA
     }
 
+    pdl_trigger();                                                      // the finish step may start launching
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_q) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_c) : "memory");
@@ -338,6 +339,10 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
     if (CG == 2) cluster_sync_all(); else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot_ptr;
+    // Everything above touched only this CTA's shared memory and TMEM; from here on the roles read
+    // what the prepare kernel wrote (queries, scales, zeroed words) and overwrite lists the previous
+    // finish step read: wait for the predecessor grid (no-op without programmatic launch).
+    pdl_wait();
 
     if (warp == 0) {
         // ===== TMA producer =====
@@ -672,10 +677,12 @@ static cudaError_t launch_one(const ScanArgs& a, const CUtensorMap* map_q, const
     cfg.gridDim = dim3(units * CG);
     cfg.dynamicSmemBytes = TcCfg<CG, KPT>::SMEM;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;       // see common.cuh (pdl_trigger / pdl_wait)
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = 2;
     return cudaLaunchKernelEx(&cfg, scan_tc_kernel<CG, KPT, COLLECT>, *map_q, *map_c, a.scale, a.tile_max, a.partials, a.gthr, a.gmax,
                               a.nq, a.nslots, a.capacity, a.head, kblocks, a.slots, a.slots_rem, groups,
                               COLLECT ? a.collect_cap : a.krank, a.dbg);

@@ -169,11 +169,13 @@ prepare_kernel(const float* __restrict__ q, int64_t nq, int dim, int ld, __nv_bf
                const uint64_t* __restrict__ tagmask, const int64_t* __restrict__ expires, int64_t nslots,
                int64_t capacity, int64_t cap_pad, int32_t min_prio, uint64_t req, int64_t now_us,
                float* __restrict__ scale, float* __restrict__ tile_max, uint32_t* __restrict__ zero_words,
-               int64_t n_zero_words, int32_t* __restrict__ inexact) {
+               int64_t n_zero_words, int32_t* __restrict__ inexact, int do_scale) {
+    pdl_trigger();                                                  // the scan may start its prologue now ...
+    pdl_wait();                                                     // ... and this grid waits for whatever still reads the buffers it rewrites
     const int lane = threadIdx.x & 31;
     const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
-    const int64_t ntiles = cap_pad / 256;
+    const int64_t ntiles = do_scale ? cap_pad / 256 : 0;            // 0: scale / tile_max of these filters are still valid
     const int64_t nzero = (n_zero_words + 127) / 128;               // 128 words (512 B) per item
     const int64_t items = nq + ntiles + nzero;
     if (warp == 0 && lane == 0 && inexact) *inexact = 0;
@@ -264,12 +266,11 @@ cudaError_t launch_prepare(const float* q, int64_t nq, int dim, int ld, void* qb
                            const int32_t* prio, const uint64_t* tagmask, const int64_t* expires, int64_t nslots,
                            int64_t capacity, int64_t cap_pad, int32_t min_prio, uint64_t req, int64_t now_us,
                            float* scale, float* tile_max, uint32_t* zero_words, int64_t n_zero_words,
-                           int32_t* inexact, cudaStream_t st) {
-    const int64_t items = nq + cap_pad / 256 + (n_zero_words + 127) / 128;
-    prepare_kernel<<<grid_for(items, 8, 148 * 8), 256, 0, st>>>(
-        q, nq, dim, ld, (__nv_bfloat16*)qb, inv_norm, prio, tagmask, expires, nslots, capacity, cap_pad, min_prio, req,
-        now_us, scale, tile_max, zero_words, n_zero_words, inexact);
-    return cudaGetLastError();
+                           int32_t* inexact, bool do_scale, cudaStream_t st) {
+    const int64_t items = nq + (do_scale ? cap_pad / 256 : 0) + (n_zero_words + 127) / 128;
+    return launch_pdl(prepare_kernel, dim3(grid_for(items, 8, 148 * 8)), dim3(256), 0, st,
+                      q, nq, dim, ld, (__nv_bfloat16*)qb, inv_norm, prio, tagmask, expires, nslots, capacity, cap_pad, min_prio, req,
+                      now_us, scale, tile_max, zero_words, n_zero_words, inexact, do_scale ? 1 : 0);
 }
 
 cudaError_t launch_compact_flags(const int64_t* expires, int64_t count, int64_t head,
