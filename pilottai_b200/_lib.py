@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpilott_b200.so")
+LIB_PATH = os.environ.get("PILOTT_B200_LIB") or os.path.join(_HERE, "libpilott_b200.so")   # override: A/B runs of two builds
 
 OK, EINVAL, ECUDA, ENOMEM, EUNSUPPORTED = 0, -1, -2, -3, -4
 MAX_FUSED_K = 32

@@ -393,7 +393,11 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
             for (int64_t t = t_lo; t < t_hi; ++t) {
                 long long c0 = (dbg & 4) ? clock64() : 0;
                 mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
-                if (dbg & 4) w_tempty += clock64() - c0;
+                if (dbg & 4) {
+                    const long long w = clock64() - c0;
+                    w_tempty += w;
+                    if (blockIdx.x == 0 && w > 1500) printf("[mma cta 0] tile %d waited %lld cyc for a free accumulator (at %lld)\n", (int)(t - t_lo), w, clock64() - t_start);
+                }
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + as * BN;
                 for (int kb = 0; kb < kblocks; ++kb) {
@@ -444,6 +448,8 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
         const int nlists_q = min(slots_g * EPI_SETS, GMAX_LISTS);
         const bool cold = !COLLECT && nlists_q >= krank && !(dbg & 16);
         const int cold_need = max(krank, nlists_q - 4);
+        const int my_list = slot * EPI_SETS + set;
+        float rowmax = -INFINITY, pubmax = -INFINITY;             // this list's best score so far for this row / what it last published
         long long w_tfull = 0, t_start = (dbg & 4) ? clock64() : 0;
         int n_prune = 0, n_slow = 0;
         long long t_prune = 0, t_slow = 0, t_loop = 0, t_early = 0;
@@ -472,7 +478,7 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
             // the query's global krank-th best (krank distinct rows reach it), so it becomes the initial
             // threshold; pass B is the normal scan of the same (still resident) accumulator tile.
             if (ti == 0 && cold && !(dbg & 1) && !a_pad) {
-                float rowmax = -INFINITY;
+                // pass A: this list's best score over its columns of the first tile
 #pragma unroll 1
                 for (int c = set * CPS; c < (set + 1) * CPS; c += 16) {
                     uint32_t v[16];
@@ -487,15 +493,20 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
 #pragma unroll
                     for (int j = 0; j < 16; ++j) rowmax = fmaxf(rowmax, __uint_as_float(v[j]) * sc[j]);
                 }
-                const int my_list = slot * EPI_SETS + set;
                 if (my_list < GMAX_LISTS && has_q && rowmax > -INFINITY) {
                     gmax[qrow * GMAX_LISTS + my_list] = f2ord(rowmax);
+                    pubmax = rowmax;
                     __threadfence();
                 }
+                // krank-th largest of the maxima the lists sweeping this query have published: krank
+                // distinct rows reach it, so it bounds the query's global krank-th best from below.
+                // (A cheaper, weaker bound here was measured and lost: the first tiles are where a low
+                // threshold costs most -- every row collects candidates and prunes.)
                 uint32_t vals[32];
                 for (int attempt = 0; attempt < 64; ++attempt) {
-                    int have = 0;
+                    int have = 32;
                     if (has_q) {
+                        have = 0;
                         const uint4* gp = reinterpret_cast<const uint4*>(gmax + qrow * GMAX_LISTS);
 #pragma unroll
                         for (int u = 0; u < 8; ++u) {
@@ -507,7 +518,6 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                     } else {
 #pragma unroll
                         for (int i = 0; i < 32; ++i) vals[i] = 0u;
-                        have = 32;
                     }
                     if (__all_sync(FULL, have >= cold_need)) break;      // enough lists have published
                     __nanosleep(256);
@@ -515,15 +525,8 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                 const uint32_t tk = kth_largest_of_32(vals, krank - 1);
                 if (tk != 0u && ord2f(tk) > thr) thr = ord2f(tk);
             }
-            // One 16-column chunk: scale, test groups of 4 (one FMNMX tree + compare + vote per group;
-            // fmaxf drops NaN = filtered rows), append on the rare hit, prune full rows.
-            auto load_scale = [&](float (&sc)[16], const int c) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const float4 f = *reinterpret_cast<const float4*>(scb + c + 4 * j);   // broadcast LDS.128
-                    sc[4 * j] = f.x; sc[4 * j + 1] = f.y; sc[4 * j + 2] = f.z; sc[4 * j + 3] = f.w;
-                }
-            };
+            // One 16-column chunk: bound test on the raw accumulators, exact test and append on the
+            // rare hit, prune full rows.
             auto process = [&](const uint32_t (&v)[16], const int c) {
                 // Fast path: no per-row scale needed.  Every score of the chunk is at most
                 // max(raw accumulator) * (largest scale of the tile), or 0 when that maximum is
@@ -534,36 +537,54 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                     mx[g] = fmaxf(fmaxf(__uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1])),
                                   fmaxf(__uint_as_float(v[4 * g + 2]), __uint_as_float(v[4 * g + 3])));
                 const float mxc = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
-                if (!__any_sync(FULL, fmaxf(mxc * smax, 0.f) >= thr)) return;
+                const bool lane_hit = fmaxf(mxc * smax, 0.f) >= thr;
+                if (!__any_sync(FULL, lane_hit)) return;
                 const long long cs = (dbg & 4) ? clock64() : 0;
-                // Slow path (warp-uniform entry): exact scores with the per-row scales
-                float sc[16], s[16];
-                load_scale(sc, c);
+                // Slow path.  Only the lanes whose bound reached their threshold do anything, and
+                // they only look at the groups of four whose own bound reached it (typically one
+                // lane, one group): per-row scales for those four columns (LDS.128, same address in
+                // every active lane), exact approximate scores, append.  No further votes: the rest
+                // of the warp waits at the reconvergence point.
+                auto scan_groups = [&](const int g0) {
+                    if (lane_hit) {
 #pragma unroll
-                for (int j = 0; j < 16; ++j) s[j] = __uint_as_float(v[j]) * sc[j];
+                        for (int g = g0; g < g0 + 2; ++g) {
+                            if (fmaxf(mx[g] * smax, 0.f) >= thr) {
+                                if (dbg & 4) ++n_slow;
+                                const float4 f = *reinterpret_cast<const float4*>(scb + c + 4 * g);
+                                const float sc4[4] = {f.x, f.y, f.z, f.w};
 #pragma unroll
-                for (int g = 0; g < 4; ++g) {
-                    const float mg = fmaxf(fmaxf(s[4 * g], s[4 * g + 1]), fmaxf(s[4 * g + 2], s[4 * g + 3]));
-                    if (__any_sync(FULL, mg >= thr)) {
-                        if (dbg & 4) ++n_slow;
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            if (s[4 * g + j] >= thr) {
-                                if (COLLECT) {
-                                    const uint32_t pos = atomicAdd(gmax + qrow, 1u);
-                                    if (pos < (uint32_t)krank) cbuf[pos] = n0 + c + 4 * g + j;
-                                } else {
-                                    mine[cnt++] = ((uint64_t)f2ord(s[4 * g + j]) << 32) | (n0 + c + 4 * g + j);
+                                for (int j = 0; j < 4; ++j) {
+                                    const float sj = __uint_as_float(v[4 * g + j]) * sc4[j];
+                                    if (sj >= thr) {                      // NaN scale (filtered row): false
+                                        if (COLLECT) {
+                                            const uint32_t pos = atomicAdd(gmax + qrow, 1u);
+                                            if (pos < (uint32_t)krank) cbuf[pos] = n0 + c + 4 * g + j;
+                                        } else {
+                                            mine[cnt++] = ((uint64_t)f2ord(sj) << 32) | (n0 + c + 4 * g + j);
+                                            rowmax = fmaxf(rowmax, sj);
+                                        }
+                                    }
                                 }
                             }
                         }
                     }
-                    if (KPT == 32 && (g & 1)) {                // 32-entry lists: fullness check every 8
-                        const unsigned full = __ballot_sync(FULL, cnt > CAPT - 8);
-                        if (full) {
-                            warp_prune_rows<CAPT, KPT>(full, rows, lane, cnt, conv, thr, head32, cap32);
-                            if (((full >> lane) & 1u) && has_q) atomicMax(gthr + qrow, f2ord(thr));
-                        }
+                    __syncwarp();
+                };
+                scan_groups(0);
+                if (KPT == 32) {                               // 32-entry lists: fullness check every 8 columns
+                    const unsigned full = __ballot_sync(FULL, cnt > CAPT - 8);
+                    if (full) {
+                        warp_prune_rows<CAPT, KPT>(full, rows, lane, cnt, conv, thr, head32, cap32);
+                        if (((full >> lane) & 1u) && has_q) atomicMax(gthr + qrow, f2ord(thr));
+                    }
+                }
+                scan_groups(2);
+                if (KPT == 32) {
+                    const unsigned full = __ballot_sync(FULL, cnt > CAPT - 8);
+                    if (full) {
+                        warp_prune_rows<CAPT, KPT>(full, rows, lane, cnt, conv, thr, head32, cap32);
+                        if (((full >> lane) & 1u) && has_q) atomicMax(gthr + qrow, f2ord(thr));
                     }
                 }
                 if (dbg & 4) t_slow += clock64() - cs;
@@ -595,6 +616,10 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                 }
             }
             if (dbg & 4) t_loop += clock64() - cl;
+            if (!COLLECT && cold && rowmax > pubmax && my_list < GMAX_LISTS && has_q) {   // a new best for this list: publish it
+                gmax[qrow * GMAX_LISTS + my_list] = f2ord(rowmax);
+                pubmax = rowmax;
+            }
             // release this accumulator stage to the MMA issuer (in the leader CTA)
             tc_fence_before();
             __syncwarp();
@@ -604,6 +629,32 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
                 mbar_arrive(bar_scempty + 8 * (int)(ti % SC_RING));     // scale slot may be refilled
             }
             if (++as == ACC_STAGES) { as = 0; aphase ^= 1; }
+            // ---- threshold refresh (after tiles 1, 3, 7, 15, ...) ------------------------------
+            // The bound keeps improving as the sweep goes on: every list publishes its running
+            // maximum whenever it grows (above), and the krank-th largest of the 32 published maxima
+            // is a lower bound of the query's global krank-th best at ANY time.  It is far tighter
+            // than what the lists can tell each other through gthr (the best KPT-th entry of a single
+            // list: one list sees 1/36 of the rows), and the fraction of rows that pass the threshold
+            // falls like 1/(rows seen), so re-reading it at every power of two keeps the pass rate
+            // within 2x of what a per-tile refresh would give, for a handful of sorts per sweep --
+            // done here, after the accumulator stage went back to the MMA issuer, where the epilogue
+            // would otherwise wait for the next tile.
+            if (cold && ti > 0 && ((ti + 1) & ti) == 0 && !(dbg & (1 | 256)) && !a_pad) {
+                uint32_t vals[32];
+                if (has_q) {
+                    const uint4* gp = reinterpret_cast<const uint4*>(gmax + qrow * GMAX_LISTS);
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        const uint4 w4 = __ldcg(gp + u);
+                        vals[4 * u] = w4.x; vals[4 * u + 1] = w4.y; vals[4 * u + 2] = w4.z; vals[4 * u + 3] = w4.w;
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) vals[i] = 0u;
+                }
+                const uint32_t tk = kth_largest_of_32(vals, krank - 1);
+                if (tk != 0u && ord2f(tk) > thr) thr = ord2f(tk);
+            }
             // Idle-time pruning: if the next accumulator is not ready yet, shrink the rows that are
             // filling up now, off the critical path, so that prunes inside the column loop (which
             // hold the accumulator stage and stall the MMA issuer) become rare.
