@@ -293,16 +293,18 @@ def run_workload(name, args, ctx, full: bool):
     flags = torch.empty(NQ, dtype=torch.uint8, device=dev)
     inexact = torch.zeros(1, dtype=torch.int32, device=dev)
     pending = []
+    depth = 3 if store.exchange == "nccl" else 1
 
     def step(i: int, q=None):
         q = qpool[i % Q_POOL] if q is None else q
         if world == 1:
             loc.search_into(q, TOPK, idx, sc, sc64, inexact, flags)
             return
-        # sharded: local search, one packed all-gather (async), merge of the PREVIOUS batch -- the
-        # exchange of batch i overlaps the local search of batch i+1
-        pending.append(store.search_begin(q, TOPK, slot=i % 2))
-        if len(pending) > 1:
+        # sharded: local search, one packed all-gather (async), merge of an EARLIER batch -- the
+        # exchange of batch i overlaps the local searches of the batches behind it (three in flight
+        # with the NCCL exchange; the peer-memory exchange allows one)
+        pending.append(store.search_begin(q, TOPK, slot=i % (depth + 1)))
+        if len(pending) > depth:
             store.search_end(pending.pop(0))
 
     def drain():

@@ -3,8 +3,15 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 namespace pilott {
+
+// PILOTT_PDL=0 in the environment turns programmatic dependent launch off (plain stream order).
+inline int pdl_enabled() {
+    static const int on = [] { const char* e = getenv("PILOTT_PDL"); return (e && e[0] == '0') ? 0 : 1; }();
+    return on;
+}
 
 // Launch with programmatic stream serialization (see common.cuh: pdl_trigger / pdl_wait).
 template <typename... KArgs, typename... Args>
@@ -13,7 +20,7 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
     cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled();
     cfg.attrs = attr; cfg.numAttrs = 1;
     return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
 }

@@ -732,7 +732,7 @@ static cudaError_t launch_one(const ScanArgs& a, const CUtensorMap* map_q, const
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;       // see common.cuh (pdl_trigger / pdl_wait)
-    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled();
     cfg.attrs = attr; cfg.numAttrs = 2;
     return cudaLaunchKernelEx(&cfg, scan_tc_kernel<CG, KPT, COLLECT>, *map_q, *map_c, a.scale, a.tile_max, a.partials, a.gthr, a.gmax,
                               a.nq, a.nslots, a.capacity, a.head, kblocks, a.slots, a.slots_rem, groups,

@@ -48,6 +48,8 @@ class ShardedSemanticStore:
     def __init__(self, dim: int, capacity: int, rank: int, world: int, device: int,
                  group: Optional[dist.ProcessGroup] = None, exchange: str = "auto"):
         self.rank, self.world, self.group = rank, world, group
+        if group is None and world > 1 and exchange != "p2p" and os.environ.get("PILOTT_EXCHANGE", "nccl") != "p2p":
+            self.group = self._small_nccl_group(world)
         if exchange == "auto":
             exchange = os.environ.get("PILOTT_EXCHANGE", "nccl")
         if exchange not in ("p2p", "nccl"):
@@ -64,6 +66,25 @@ class ShardedSemanticStore:
         self.dim, self.device = dim, device
         self.total = 0                                  # global rows ever appended
         self._bufs = {}
+
+    @staticmethod
+    def _small_nccl_group(world: int):
+        """A process group of its own for the exchange, with NCCL held to one CTA.  The block
+        exchanged per step is ~160 KB, so bandwidth does not matter -- where the collective's kernel
+        RUNS does: the scan of the next batch wants 72 SM pairs of the 74, and every SM an all-gather
+        with the default channel count takes from it delays a CTA pair by the whole all-gather
+        (measured on 4 B200, 0.306 ms of local search per step: 0.358 ms per step with NCCL's default, 0.315 with one CTA).  PILOTT_NCCL_MAX_CTAS overrides (0 = default
+        group, NCCL's own choice).  Collective: every rank constructs its store at the same point."""
+        n = int(os.environ.get("PILOTT_NCCL_MAX_CTAS", "1"))
+        if n <= 0:
+            return None
+        try:
+            opts = dist.ProcessGroupNCCL.Options()
+            opts.config.max_ctas = n
+            opts.config.min_ctas = 1
+            return dist.new_group(list(range(world)), pg_options=opts)
+        except Exception:
+            return None
 
     def append(self, x, prio=None, tagmask=None, expires_us=None) -> int:
         """Every rank calls this with the SAME global batch (host numpy or CUDA tensor); each
