@@ -3,8 +3,7 @@
 # box with the snapshot) so that bench.py can time the reference's own CPU path there
 # (oracle/reference_path.py).  The reference's build backend (poetry-dynamic-versioning) is not in
 # this image, so the install runs from a copy under /tmp whose pyproject.toml names setuptools
-# instead; the package sources are not touched (diff -r pilott baseline/_ref/pilott: only the
-# non-Python `source/` data directory is left out).
+# instead; the package sources are not touched (diff -r pilott baseline/_ref/pilott: identical).
 set -e
 REF=${PILOTT_REFERENCE:-/root/reference}
 ROOT=$(cd "$(dirname "$0")/.." && pwd)
@@ -25,6 +24,9 @@ version = "0.0.0"
 
 [tool.setuptools.packages.find]
 include = ["pilott*"]
+
+[tool.setuptools.package-data]
+pilott = ["source/*"]
 '''
 open(p, 'w').write(s)
 PY

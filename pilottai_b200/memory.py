@@ -12,6 +12,15 @@ reference (pilott/memory/enhanced_memory.py); written from scratch.  What change
 * reference defects deliberately NOT reproduced: stale tag/priority
   indexes after the deque overflows (:86-87 vs :133-144), ``max()`` of an empty index on
   an empty store (:124), first-found early break.
+* concurrent ``semantic_search`` calls are COALESCED: the reference's callers issue one search per
+  coroutine (:93-99); here each call parks its query and a drain task sends everything that is
+  waiting with the same filters to the device as ONE batch (one kernel sequence for up to
+  ``coalesce_max`` queries), then hands every caller its own rows.  Signatures are unchanged and so
+  are the results: a call gets exactly what it would have got alone.
+* tags are unbounded, as in the reference (its tag index is a dict of sets, :133-138): the device
+  row carries a 64-bit tag mask, the first 63 distinct tags get a bit each, every further tag shares
+  the last bit, and a search that names such a tag is filtered on that bit by the device and on
+  the exact tag sets by the host (asking the device for more rows until ``limit`` of them survive).
 
 Host side keeps the ``MemoryItem`` objects (text, metadata) in insertion order; the device
 keeps one row per item (bf16 vector, inverse norm, priority, tag mask, expiry).  The two are
@@ -57,7 +66,12 @@ class MemoryItem(BaseModel):
 
 class EnhancedMemory:
     def __init__(self, max_size: int = 10000, cleanup_interval: int = 3600, *, dim: int = 768,
-                 device: int = 0, embedder=None):
+                 device: int = 0, embedder=None, coalesce_max: int = 256, coalesce_window_s: float = 0.0):
+        self.coalesce_max = int(coalesce_max)            # queries per device batch of coalesced single searches
+        self.coalesce_window_s = float(coalesce_window_s)  # extra wait for company before a batch leaves (0: one loop turn)
+        self._waiting: List[tuple] = []                  # parked single searches: (vector, k, mask, min_priority, future)
+        self._drain_task: Optional[asyncio.Task] = None
+        self.coalesced_batches = 0                       # device batches the drain task has sent (bookkeeping for tests)
         self.max_size = int(max_size)
         self.dim = int(dim)
         self._items: deque = deque(maxlen=self.max_size)       # MemoryItem, oldest first
@@ -92,14 +106,14 @@ class EnhancedMemory:
         self._store.close()
 
     # ---- tags -> bits ---------------------------------------------------------------------
+    _OVERFLOW_BIT = MAX_TAGS - 1                          # shared by every tag after the first 63
+
     def _mask_for_store(self, tags: Iterable[str]) -> int:
         m = 0
         for t in tags:
             b = self._tag_bits.get(t)
             if b is None:
-                if len(self._tag_bits) >= MAX_TAGS:
-                    raise ValueError(f"more than {MAX_TAGS} distinct tags")
-                b = self._tag_bits[t] = len(self._tag_bits)
+                b = self._tag_bits[t] = min(len(self._tag_bits), self._OVERFLOW_BIT)
             m |= 1 << b
         return m
 
@@ -112,6 +126,10 @@ class EnhancedMemory:
                 return None
             m |= 1 << b
         return m
+
+    def _needs_host_filter(self, tags: Optional[Iterable[str]]) -> bool:
+        """True when a requested tag shares the overflow bit: the device filter is then only necessary."""
+        return any(self._tag_bits.get(t) == self._OVERFLOW_BIT and len(self._tag_bits) > MAX_TAGS - 1 for t in tags or ())
 
     # ---- store (reference :60-91) ---------------------------------------------------------
     async def store_semantic(self, text: str, metadata: Optional[Dict[str, Any]] = None,
@@ -160,16 +178,84 @@ class EnhancedMemory:
         base = self._store.total - len(self._items)
         return self._items[seq - base]
 
+    async def _device_search(self, q: np.ndarray, k: int, req: int, min_priority: int):
+        async with self._semantic_lock:
+            now_us = _to_us(datetime.now())
+            return await asyncio.to_thread(self._store.search, q, k, min_priority, req, now_us)
+
     async def semantic_search_batch(self, queries, k: int = 5, tags: Optional[Set[str]] = None,
                                     min_priority: int = 0) -> Tuple[np.ndarray, np.ndarray]:
         """queries [Q, dim] fp32 -> (insertion sequence numbers [Q,k] (-1 = none), scores [Q,k])."""
         q = np.ascontiguousarray(queries, dtype=np.float32).reshape(-1, self.dim)
         req = self._mask_for_query(tags)
+        if req is None or k < 1:
+            return (np.full((q.shape[0], max(k, 0)), -1, np.int64), np.full((q.shape[0], max(k, 0)), -np.inf, np.float32))
+        if not self._needs_host_filter(tags):
+            return await self._device_search(q, k, req, min_priority)
+        # A requested tag shares the overflow bit: the device narrows to rows carrying SOME overflow tag,
+        # the exact tag sets decide.  Ask for more rows until k survive (or the store is exhausted).
+        want = set(tags)
+        out_i = np.full((q.shape[0], k), -1, np.int64)
+        out_s = np.full((q.shape[0], k), -np.inf, np.float32)
+        todo = np.arange(q.shape[0])
+        kk = max(4 * k, 64)
+        while todo.size:
+            kk = min(kk, max(len(self._items), 1))
+            idx, sc = await self._device_search(q[todo], kk, req, min_priority)
+            again = []
+            for r, qi in enumerate(todo):
+                keep = [j for j in range(kk) if idx[r, j] >= 0 and want <= self._item_for_seq(int(idx[r, j])).tags]
+                exhausted = kk >= len(self._items) or idx[r, kk - 1] < 0
+                if len(keep) >= k or exhausted:
+                    keep = keep[:k]
+                    out_i[qi, :len(keep)] = idx[r, keep]
+                    out_s[qi, :len(keep)] = sc[r, keep]
+                else:
+                    again.append(qi)
+            todo = np.array(again, dtype=np.int64)
+            kk *= 4
+        return out_i, out_s
+
+    # -- coalescing of single searches ------------------------------------------------------
+    async def _search_one(self, vec: np.ndarray, k: int, tags: Optional[Set[str]], min_priority: int):
+        """One query through the shared batch: parks it, makes sure the drain task runs, awaits its rows."""
+        req = self._mask_for_query(tags)
         if req is None:
-            return (np.full((q.shape[0], k), -1, np.int64), np.full((q.shape[0], k), -np.inf, np.float32))
-        async with self._semantic_lock:
-            now_us = _to_us(datetime.now())
-            return await asyncio.to_thread(self._store.search, q, k, min_priority, req, now_us)
+            return np.full(k, -1, np.int64), np.full(k, -np.inf, np.float32)
+        if self._needs_host_filter(tags):                # rare path: exact tag sets are checked on the host
+            idx, sc = await self.semantic_search_batch(vec[None], k, tags, min_priority)
+            return idx[0], sc[0]
+        fut = asyncio.get_running_loop().create_future()
+        self._waiting.append((vec, k, req, min_priority, fut))
+        if self._drain_task is None or self._drain_task.done():
+            self._drain_task = asyncio.create_task(self._drain())
+        return await fut
+
+    async def _drain(self):
+        """Sends whatever is parked, grouped by filter, `coalesce_max` queries at a time.  Callers that
+        arrive while a batch is on the device are picked up by the next turn of the loop."""
+        await asyncio.sleep(0)                            # one loop turn: every coroutine that is ready parks its query
+        if self.coalesce_window_s > 0 and len(self._waiting) < self.coalesce_max:
+            await asyncio.sleep(self.coalesce_window_s)
+        while self._waiting:
+            batch, self._waiting = self._waiting, []
+            groups: Dict[tuple, list] = {}
+            for w in batch:                               # same filters, same side of the fused-path limit
+                groups.setdefault((w[2], w[3], w[1] > 32), []).append(w)
+            for (req, min_priority, _), ws in groups.items():
+                for lo in range(0, len(ws), self.coalesce_max):
+                    part = ws[lo:lo + self.coalesce_max]
+                    try:
+                        k = max(w[1] for w in part)
+                        idx, sc = await self._device_search(np.stack([w[0] for w in part]), k, req, min_priority)
+                        self.coalesced_batches += 1
+                        for r, w in enumerate(part):      # the top-k of a total order is a prefix of the top-k'
+                            if not w[4].done():
+                                w[4].set_result((idx[r, :w[1]], sc[r, :w[1]]))
+                    except Exception as e:
+                        for w in part:
+                            if not w[4].done():
+                                w[4].set_exception(e)
 
     async def semantic_search(self, query: str, tags: Optional[Set[str]] = None, min_priority: int = 0,
                               limit: int = 5, *, query_embedding=None, order: str = "priority") -> List[MemoryItem]:
@@ -179,8 +265,8 @@ class EnhancedMemory:
             if limit < 1:
                 return []
             q = self._embed(query) if query_embedding is None else np.asarray(query_embedding, np.float32)
-            idx, _ = await self.semantic_search_batch(q[None], limit, tags, min_priority)
-            found = [self._item_for_seq(int(s)) for s in idx[0] if s >= 0]
+            idx, _ = await self._search_one(np.ascontiguousarray(q, np.float32).reshape(self.dim), limit, tags, min_priority)
+            found = [self._item_for_seq(int(s)) for s in idx if s >= 0]
             if order == "score":
                 return found
             return sorted(found, key=lambda x: (-x.priority, x.timestamp))       # reference :114

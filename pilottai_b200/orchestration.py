@@ -59,14 +59,24 @@ class _EngineCache:
     """Keeps a RoutingEngine per agent population; metrics are re-snapshotted every pass."""
 
     def __init__(self, device: int):
-        self.device, self._eng = device, None
+        self.device, self._eng, self._sig = device, None, None
 
     async def snapshot(self, agents: Sequence[Any], extra=None) -> Tuple[RoutingEngine, List[dict]]:
         rows = [await features_from_agent(a) for a in agents]
         if extra:
             for r in rows:
                 r.update(extra.get(r["id"], {}))
-        self._eng = RoutingEngine(rows, self.device)       # tables are small (KBs); rebuilt per pass
+        # The device-resident part of the engine (vocabularies, capability / specialization bit sets)
+        # depends only on who the agents are and what they can do; it is rebuilt when that changes.
+        # The metrics are new every pass: they only enter the per-agent score terms, which the
+        # engine derives from `agents` on the first call of each pass.
+        sig = tuple((r["id"], None if r["caps"] is None else tuple(r["caps"]),
+                     None if r["specializations"] is None else tuple(r["specializations"])) for r in rows)
+        if self._eng is None or self._sig != sig:
+            self._eng, self._sig = RoutingEngine(rows, self.device), sig
+        else:
+            self._eng.agents = rows
+            self._eng._tables.clear()
         return self._eng, rows
 
 
@@ -244,14 +254,33 @@ class LoadBalancer:
         return (loads[-1] - loads[0]) / len(loads)
 
     async def _analyze_agent_loads(self, current_metrics: Dict[str, LoadMetrics]) -> Tuple[List[str], List[str]]:   # :143-159
-        over, under = [], []
-        for aid, m in current_metrics.items():
-            trend, load = self._calculate_load_trend(aid), self._calculate_composite_load(m)
-            if load > self.config.overload_threshold and trend > 0:
-                over.append(aid)
-            elif load < self.config.underload_threshold and trend < 0:
-                under.append(aid)
-        return over, under
+        """Classification of every agent in one pass of array arithmetic (the reference walks the
+        agents one by one): composite load of the current sample and of the first / last of the
+        five newest history samples, trend = (last - first) / samples, over = load > overload
+        threshold and rising, under = load < underload threshold and falling.  numpy evaluates the
+        same fp64 operations in the same order as the scalar code (lb_composite), so the two
+        lists are the reference's, in its order."""
+        import numpy as np
+        ids = list(current_metrics)
+        if not ids:
+            return [], []
+        mt = self.config.max_tasks_per_agent
+
+        def comp(ms):
+            a = np.array([(m.cpu_usage, m.memory_usage, m.queue_size, m.error_rate) for m in ms], dtype=np.float64).reshape(-1, 4)
+            return 0.3 * a[:, 0] + 0.3 * a[:, 1] + 0.2 * (a[:, 2] / mt) + 0.2 * a[:, 3]
+
+        hists = [self._metrics_history.get(aid, [])[-5:] for aid in ids]
+        n = np.array([len(h) for h in hists], dtype=np.int64)
+        have = n >= 2
+        first = comp([h[0] for h, ok in zip(hists, have) if ok])
+        last = comp([h[-1] for h, ok in zip(hists, have) if ok])
+        trend = np.zeros(len(ids), np.float64)
+        trend[have] = (last - first) / n[have]
+        load = comp([current_metrics[aid] for aid in ids])
+        over = (load > self.config.overload_threshold) & (trend > 0)
+        under = (load < self.config.underload_threshold) & (trend < 0) & ~over
+        return [ids[i] for i in np.nonzero(over)[0]], [ids[i] for i in np.nonzero(under)[0]]
 
     async def _find_best_agents(self, tasks: Sequence[Dict], candidates: List[str],
                                 current_metrics: Dict[str, LoadMetrics]) -> List[Optional[str]]:

@@ -291,3 +291,119 @@ def test_load_balancer_redistribution_matches_reference(torch_cuda, golden_dir):
                     for a in kids.values() for t in a.tasks.values() if "moved_to" in t), key=lambda m: m["task"])
     assert moved == g["result"]["moved"]
     assert {aid: list(a.tasks.keys()) for aid, a in kids.items()} == g["result"]["queues_after"]
+
+
+def _reference_or_skip():
+    """The unmodified reference package: /root/reference in the build container, baseline/_ref
+    (oracle/install_reference.sh) on the GPU box."""
+    import sys
+    from oracle import reference_path
+    ref = reference_path.locate()
+    if ref is None:
+        pytest.skip("no reference package on this machine (baseline/_ref not installed)")
+    os.environ["PILOTT_REFERENCE"] = ref
+    if ref not in sys.path:
+        sys.path.insert(0, ref)
+    return ref
+
+
+def test_adapter_on_the_real_reference_serve(torch_cuda, golden_dir):
+    """SURVEY section 8(f) N1 on the reference's own classes: a real `pilott.Serve` over real
+    `BaseAgent`s (psutil readings replaced per agent, as in the fixture run), real `Task` /
+    `TaskResult` models.  After attach(), `Serve._select_agent` must return the agent the
+    unmodified reference router picked for the same task (tests/golden/routing_mid.json), or the
+    reference's own default pick where the router finds nobody (pilott.py:494-496), and
+    `Serve._update_memory` must land in both memories."""
+    _reference_or_skip()
+    import logging
+    from oracle import gen_golden
+    from pilott import Serve
+    from pilott.core.task import Task, TaskResult
+    from pilottai_b200.serve_adapter import attach
+    g = _load(golden_dir, "mid")
+    workers = gen_golden.build_reference_agents(g["agents"])
+    logging.disable(logging.CRITICAL)
+
+    async def scenario():
+        serve = Serve(agents=workers, manager_llm=object())
+        assert list(serve.agents) == [r["id"] for r in g["agents"]]          # dict role -> agent (pilott.py:93)
+        default = await serve._select_agent(None)                              # reference behaviour before attach
+        router, mem = attach(serve, device=0)
+        n, routed = 60, 0
+        for t, want in zip(g["tasks"][:n], g["router"][:n]):
+            meta = {k: t[k] for k in ("type", "required_capabilities", "tags", "urgent") if k in t}
+            # (dependencies stay empty: the reference's cycle check rejects any non-empty list of
+            #  plain ids, task.py:121-134; they do not enter the routing score)
+            task = Task(description=f"task {t['id']}", metadata=meta, complexity=t.get("complexity"))
+            got = await serve._select_agent(task)
+            if want["agent"] is None:
+                assert got is default
+            else:
+                assert got.id == want["agent"]
+                routed += 1
+        assert routed > n // 2
+        task = Task(description="summarise the quarterly pdf report", metadata={"type": "spec03"})
+        await serve._update_memory(task, TaskResult(success=True, output="done", execution_time=0.1))
+        assert len(mem) == 1 and workers[0].enhanced_memory is mem
+        kept = serve.memory.retrieve({"type": "task_execution"})                # the reference's own memory got it too
+        if asyncio.iscoroutine(kept):
+            kept = await kept
+        assert len(kept) == 1
+        hit = await workers[3].enhanced_memory.semantic_search("quarterly pdf report summary", limit=1)
+        assert hit[0].metadata["task_id"] == task.id and hit[0].priority == 1
+        mem.close()
+    try:
+        asyncio.run(scenario())
+    finally:
+        logging.disable(logging.NOTSET)
+
+
+def test_thousand_concurrent_single_searches(torch_cuda):
+    """Reference callers issue one semantic_search per coroutine (enhanced_memory.py:93-99).  1000 of
+    them in flight are served by a handful of device batches and each gets exactly what it gets alone."""
+    import time
+    from pilottai_b200 import EnhancedMemory
+
+    async def scenario():
+        rng = np.random.default_rng(3)
+        n, dim = 20_000, 256
+        mem = EnhancedMemory(max_size=n, dim=dim)
+        emb = rng.standard_normal((n, dim)).astype(np.float32)
+        await mem.store_semantic_batch([f"note {i}" for i in range(n)], emb,
+                                       tags=[{"even"} if i % 2 == 0 else {"odd"} for i in range(n)],
+                                       priority=[i % 4 for i in range(n)])
+        qs = rng.standard_normal((1000, dim)).astype(np.float32)
+        kw = [dict(limit=1 + i % 9, tags=({"even"} if i % 3 == 0 else None), min_priority=i % 2) for i in range(1000)]
+        await mem.semantic_search("warm", query_embedding=qs[0])
+        b0, t0 = mem.coalesced_batches, time.perf_counter()
+        got = await asyncio.gather(*[mem.semantic_search("q", query_embedding=qs[i], order="score", **kw[i]) for i in range(1000)])
+        dt = time.perf_counter() - t0
+        assert mem.coalesced_batches - b0 <= 12
+        t1 = time.perf_counter()
+        for i in range(0, 1000, 10):
+            alone = await mem.semantic_search("q", query_embedding=qs[i], order="score", **kw[i])
+            assert [x.text for x in alone] == [x.text for x in got[i]] and len(alone) == kw[i]["limit"]
+        dt_alone = (time.perf_counter() - t1) / 100
+        print(f"\\n1000 concurrent semantic_search: {1000 / dt:.0f} q/s in {mem.coalesced_batches - b0} device batches; "
+              f"one at a time: {1 / dt_alone:.0f} q/s")
+        mem.close()
+    asyncio.run(scenario())
+
+
+def test_more_than_64_tags_on_the_device_store(torch_cuda):
+    from pilottai_b200 import EnhancedMemory
+
+    async def scenario():
+        rng = np.random.default_rng(4)
+        n, dim = 500, 64
+        mem = EnhancedMemory(max_size=1000, dim=dim)
+        emb = rng.standard_normal((n, dim)).astype(np.float32)
+        tags = [{f"tag{i % 120}", f"grp{i % 3}"} for i in range(n)]
+        await mem.store_semantic_batch([f"item {i}" for i in range(n)], emb, tags=tags)
+        q = rng.standard_normal(dim).astype(np.float32)
+        for want in ({"tag5"}, {"tag100"}, {"tag119", "grp2"}, {"tag70", "tag71"}, {"never"}):
+            got = await mem.semantic_search("q", tags=want, limit=20, query_embedding=q)
+            expect = {i for i in range(n) if want <= tags[i]}
+            assert {int(x.text.split()[1]) for x in got} <= expect and len(got) == min(20, len(expect))
+        mem.close()
+    asyncio.run(scenario())

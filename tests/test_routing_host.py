@@ -171,3 +171,48 @@ def test_c_task_encoder_equals_the_python_definition():
     want = routing.encode_tasks(odd, vocab)
     for k in want:
         assert np.array_equal(got[k], want[k]), k
+
+
+import pytest as _pytest
+
+
+@_pytest.mark.parametrize("case", ["mid", "wide", "small"])
+def test_vectorised_load_classification_matches_reference_fixture(golden_dir, case):
+    """LoadBalancer._analyze_agent_loads as array arithmetic against what the
+    unmodified reference returned for the same histories (tests/golden/routing_*.json), plus 1024
+    agents against the scalar statement of the same rule (load_balancer.py:143-170)."""
+    import asyncio, json, os
+    import numpy as np
+    from pilottai_b200 import LoadBalancer, LoadMetrics
+    from pilottai_b200.routing import lb_composite
+    with open(os.path.join(golden_dir, f"routing_{case}.json")) as f:
+        g = json.load(f)
+    lbg = g["load_balancer"]
+
+    class Orch:
+        child_agents = {}
+    lb = LoadBalancer(Orch(), g["lb_config"])
+    for aid, h in lbg["history"].items():
+        lb._metrics_history[aid] = [LoadMetrics(**m) for m in h]
+    current = {aid: lb._metrics_history[aid][-1] for aid in lbg["history"]}
+    over, under = asyncio.run(lb._analyze_agent_loads(current))
+    assert over == lbg["overloaded"] and under == lbg["underloaded"]
+    if case != "mid":
+        return
+    rng = np.random.default_rng(11)
+    lb2 = LoadBalancer(Orch(), {"max_tasks_per_agent": 60, "overload_threshold": 0.6, "underload_threshold": 0.4})
+    cur = {}
+    for i in range(1024):
+        hist = [LoadMetrics(cpu_usage=float(rng.random()), memory_usage=float(rng.random()), queue_size=int(rng.integers(0, 70)),
+                            error_rate=float(rng.random())) for _ in range(int(rng.integers(1, 8)))]
+        lb2._metrics_history[f"a{i}"] = hist
+        cur[f"a{i}"] = hist[-1]
+    over, under = asyncio.run(lb2._analyze_agent_loads(cur))
+    want_over, want_under = [], []
+    for aid, m in cur.items():
+        load, trend = lb2._calculate_composite_load(m), lb2._calculate_load_trend(aid)
+        if load > 0.6 and trend > 0:
+            want_over.append(aid)
+        elif load < 0.4 and trend < 0:
+            want_under.append(aid)
+    assert over == want_over and under == want_under and over and under
