@@ -293,7 +293,7 @@ def run_workload(name, args, ctx, full: bool):
     flags = torch.empty(NQ, dtype=torch.uint8, device=dev)
     inexact = torch.zeros(1, dtype=torch.int32, device=dev)
     pending = []
-    depth = 3 if store.exchange == "nccl" else 1
+    depth = 1 if store.exchange == "p2p" else 3      # batches in flight behind the one being searched
 
     def step(i: int, q=None):
         q = qpool[i % Q_POOL] if q is None else q
@@ -301,16 +301,16 @@ def run_workload(name, args, ctx, full: bool):
             loc.search_into(q, TOPK, idx, sc, sc64, inexact, flags)
             return
         # sharded: local search, one packed all-gather (async), merge of an EARLIER batch -- the
-        # exchange of batch i overlaps the local searches of the batches behind it (three in flight
-        # with the NCCL exchange; the peer-memory exchange allows one)
+        # exchange of batch i overlaps the local searches of the batches behind it; the merge kernel
+        # runs on the store's side stream (wait=False: nothing on this stream consumes the result)
         pending.append(store.search_begin(q, TOPK, slot=i % (depth + 1)))
         if len(pending) > depth:
-            store.search_end(pending.pop(0))
+            store.search_end(pending.pop(0), wait=False)
 
     def drain():
         out = None
         while pending:
-            out = store.search_end(pending.pop(0))
+            out = store.search_end(pending.pop(0))       # (waits for the merge: the caller reads the result)
         return out
 
     def barrier():
@@ -475,9 +475,8 @@ def run_workload(name, args, ctx, full: bool):
 
             def finish(j):
                 s = j % NSLOT
-                store.search_end(tickets[s])                         # merge into the slot's packed result block
-                ev_done[s].record(main)
-                d2h_s.wait_event(ev_done[s])
+                store.search_end(tickets[s], wait=False)             # merge (side stream) into the slot's packed result block
+                d2h_s.wait_event(tickets[s][0]["merged"])
                 with torch.cuda.stream(d2h_s):
                     out_p[s].copy_(tickets[s][0]["pack"], non_blocking=True)    # ONE D2H: indices, scores, counter
                 ev_d2h[s].record(d2h_s)

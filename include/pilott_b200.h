@@ -232,14 +232,21 @@ int pilott_mem_export(pilott_mem_t* h, uint16_t* vec_bits_host, float* inv_norm_
  * releases a per-(slot, rank) flag there, and the merge kernel acquires the flags of its slot
  * before it ranks the world*k candidates of each query.  No reference counterpart (the
  * reference is single-process).
- *   create : allocates [4 slots][world][block_bytes] + flags on `device`; handle_out receives
+ *   create : allocates [8 slots][world][block_bytes] + flags on `device`; handle_out receives
  *            PILOTT_IPC_HANDLE_BYTES bytes to hand to the other ranks (any transport).
  *   connect: handles = world * PILOTT_IPC_HANDLE_BYTES bytes in rank order (own entry ignored).
  *   publish: block_dev = this rank's block (bytes <= block_bytes, multiple of 16), step >= 0.
+ *   publish_copy: the same block and flag, written by the copy engines (cudaMemcpyAsync into each
+ *            peer's buffer on a stream the exchange owns, ordered behind `stream`): no kernel, so
+ *            no SM is taken from the scan of the next batch -- on B200 the pair scan needs all 72
+ *            SM pairs a GPU has, and one CTA of a collective's kernel on the wrong SM delays one
+ *            pair by the whole collective.  buffer_id (0..7) names the caller's block buffer: call
+ *            pilott_xchg_wait_buffer(x, buffer_id, stream) before the next search overwrites it.
  *   merge  : waits for every rank's block of `step`, writes the global top-k like
- *            pilott_topk_merge_packed.  Per rank, publish(s+1) may be enqueued before merge(s)
- *            (one batch of overlap), but publish(s+2) must follow merge(s): that rule is what
- *            makes the four slots enough.  Every rank must take part in every step.
+ *            pilott_topk_merge_packed.  Per rank, up to three publishes may be enqueued ahead of
+ *            the oldest outstanding merge (publish(s+1..s+3) before merge(s)), but publish(s+4)
+ *            must follow merge(s): that rule is what makes the eight slots enough.  Every rank
+ *            must take part in every step.
  *   check  : synchronises the device and reports whether any merge gave up waiting (2 s) for
  *            a peer -- such a merge wrote "no result" rows instead of hanging. */
 #define PILOTT_IPC_HANDLE_BYTES 64
@@ -248,6 +255,9 @@ int pilott_xchg_create(int device, int rank, int world, int64_t block_bytes, pil
                        void* handle_out);
 int pilott_xchg_connect(pilott_xchg_t* x, const void* handles);
 int pilott_xchg_publish(pilott_xchg_t* x, const void* block_dev, int64_t bytes, int64_t step, void* stream);
+int pilott_xchg_publish_copy(pilott_xchg_t* x, const void* block_dev, int64_t bytes, int64_t step, int buffer_id,
+                             void* stream);
+int pilott_xchg_wait_buffer(pilott_xchg_t* x, int buffer_id, void* stream);
 int pilott_xchg_merge(pilott_xchg_t* x, int64_t step, int64_t nq, int k, int64_t* out_idx_dev,
                       float* out_score_dev, double* out_score64_dev, void* stream);
 /* pilott_mem_search + publish in one: finish_kernel stores each query's result row straight into

@@ -53,6 +53,8 @@ SIGNATURES = {
     "pilott_xchg_create": (C.c_int, [C.c_int, C.c_int, C.c_int, c_i64, C.POINTER(c_vp), c_vp]),
     "pilott_xchg_connect": (C.c_int, [c_vp, c_vp]),
     "pilott_xchg_publish": (C.c_int, [c_vp, c_vp, c_i64, c_i64, c_vp]),
+    "pilott_xchg_publish_copy": (C.c_int, [c_vp, c_vp, c_i64, c_i64, C.c_int, c_vp]),
+    "pilott_xchg_wait_buffer": (C.c_int, [c_vp, C.c_int, c_vp]),
     "pilott_xchg_merge": (C.c_int, [c_vp, c_i64, c_i64, C.c_int, c_vp, c_vp, c_vp, c_vp]),
     "pilott_mem_search_publish": (C.c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, C.c_int, c_i32, c_u64, c_i64, c_vp, c_vp,
                                             c_vp, c_vp, c_vp, c_vp]),

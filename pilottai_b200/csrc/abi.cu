@@ -188,6 +188,14 @@ struct pilott_xchg {
     int32_t* err_dev = nullptr;
     uint32_t* done_dev = nullptr;            // CTA arrival counter of the fused finish + publish
     bool connected = false;
+    // publish by copy: a stream of its own for the copy engines, the flag values as a constant
+    // table in device memory (entry i holds i + 1: a copy engine reads its source when the copy
+    // RUNS, possibly many steps after it was enqueued, so the source must never change), one
+    // event per caller buffer
+    cudaStream_t copy_stream = nullptr;
+    uint64_t* flag_vals = nullptr;
+    cudaEvent_t ev_ready = nullptr;
+    cudaEvent_t ev_buf[8] = {};
 };
 
 namespace {
@@ -1257,8 +1265,8 @@ int pilott_xchg_create(int device, int rank, int world, int64_t block_bytes, pil
     DeviceGuard g(device);
     auto* x = new pilott_xchg();
     x->device = device; x->rank = rank; x->world = world; x->block_bytes = block_bytes;
-    x->flags_off = 4 * (int64_t)world * block_bytes;                 // 4 slots (see xchg.cu)
-    x->total_bytes = x->flags_off + 4 * (int64_t)world * 8;
+    x->flags_off = pilott::XCHG_SLOTS * (int64_t)world * block_bytes;     // see xchg.cu
+    x->total_bytes = x->flags_off + pilott::XCHG_SLOTS * (int64_t)world * 8;
     cudaError_t e = cudaMalloc(&x->mine, (size_t)x->total_bytes);
     if (e == cudaSuccess) e = cudaMemset(x->mine, 0, (size_t)x->total_bytes);
     if (e == cudaSuccess) e = cudaMalloc(&x->peers_dev, (size_t)world * sizeof(void*));
@@ -1266,11 +1274,23 @@ int pilott_xchg_create(int device, int rank, int world, int64_t block_bytes, pil
     if (e == cudaSuccess) e = cudaMemset(x->err_dev, 0, 4);
     if (e == cudaSuccess) e = cudaMalloc(&x->done_dev, 4);
     if (e == cudaSuccess) e = cudaMemset(x->done_dev, 0, 4);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&x->copy_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&x->flag_vals, pilott::XCHG_FLAG_RING * sizeof(uint64_t));
+    if (e == cudaSuccess) {
+        std::vector<uint64_t> vals((size_t)pilott::XCHG_FLAG_RING);
+        for (int i = 0; i < pilott::XCHG_FLAG_RING; ++i) vals[(size_t)i] = (uint64_t)i + 1;
+        e = cudaMemcpy(x->flag_vals, vals.data(), vals.size() * sizeof(uint64_t), cudaMemcpyHostToDevice);
+    }
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&x->ev_ready, cudaEventDisableTiming);
+    for (int i = 0; i < 8 && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&x->ev_buf[i], cudaEventDisableTiming);
     cudaIpcMemHandle_t hnd;
     if (e == cudaSuccess) e = cudaIpcGetMemHandle(&hnd, x->mine);
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
     if (e != cudaSuccess) {
-        cudaFree(x->mine); cudaFree(x->peers_dev); cudaFree(x->err_dev); cudaFree(x->done_dev);
+        cudaFree(x->mine); cudaFree(x->peers_dev); cudaFree(x->err_dev); cudaFree(x->done_dev); cudaFree(x->flag_vals);
+        if (x->copy_stream) cudaStreamDestroy(x->copy_stream);
+        if (x->ev_ready) cudaEventDestroy(x->ev_ready);
+        for (cudaEvent_t ev : x->ev_buf) if (ev) cudaEventDestroy(ev);
         delete x;
         return fail_cuda(e, "pilott_xchg_create");
     }
@@ -1332,6 +1352,39 @@ int pilott_xchg_publish(pilott_xchg_t* x, const void* block_dev, int64_t bytes, 
     return PILOTT_OK;
 }
 
+int pilott_xchg_publish_copy(pilott_xchg_t* x, const void* block_dev, int64_t bytes, int64_t step, int buffer_id,
+                             void* stream) {
+    if (!x || !block_dev) return fail(PILOTT_EINVAL, "NULL pointer");
+    if (!x->connected) return fail(PILOTT_EINVAL, "exchange is not connected");
+    if (bytes < 16 || bytes % 16 || bytes > x->block_bytes) return fail(PILOTT_EINVAL, "bytes must be a multiple of 16 within block_bytes");
+    if (step < 0) return fail(PILOTT_EINVAL, "step is negative");
+    if (buffer_id < 0 || buffer_id >= 8) return fail(PILOTT_EINVAL, "buffer_id must be in [0, 8)");
+    DeviceGuard g(x->device);
+    const int slot = (int)(step & (pilott::XCHG_SLOTS - 1));
+    // the block is complete when `stream` gets here; the copies run beside whatever `stream` does next
+    CK(cudaEventRecord(x->ev_ready, (cudaStream_t)stream));
+    CK(cudaStreamWaitEvent(x->copy_stream, x->ev_ready, 0));
+    for (int i = 0; i < x->world; ++i) {
+        const int r = (x->rank + i) % x->world;           // every rank starts with a different destination
+        unsigned char* base = x->peers[r];
+        CK(cudaMemcpyAsync(base + ((int64_t)slot * x->world + x->rank) * x->block_bytes, block_dev, (size_t)bytes,
+                           cudaMemcpyDeviceToDevice, x->copy_stream));
+        // same stream: the flag lands after the block it announces
+        CK(cudaMemcpyAsync(base + x->flags_off + ((int64_t)slot * x->world + x->rank) * 8, x->flag_vals + (step & (pilott::XCHG_FLAG_RING - 1)), 8,
+                           cudaMemcpyDeviceToDevice, x->copy_stream));
+    }
+    CK(cudaEventRecord(x->ev_buf[buffer_id], x->copy_stream));
+    return PILOTT_OK;
+}
+
+int pilott_xchg_wait_buffer(pilott_xchg_t* x, int buffer_id, void* stream) {
+    if (!x) return fail(PILOTT_EINVAL, "NULL pointer");
+    if (buffer_id < 0 || buffer_id >= 8) return fail(PILOTT_EINVAL, "buffer_id must be in [0, 8)");
+    DeviceGuard g(x->device);
+    CK(cudaStreamWaitEvent((cudaStream_t)stream, x->ev_buf[buffer_id], 0));      // a never-recorded event is complete
+    return PILOTT_OK;
+}
+
 int pilott_xchg_merge(pilott_xchg_t* x, int64_t step, int64_t nq, int k, int64_t* out_idx_dev, float* out_score_dev,
                       double* out_score64_dev, void* stream) {
     if (!x) return fail(PILOTT_EINVAL, "NULL pointer");
@@ -1362,6 +1415,10 @@ int pilott_xchg_destroy(pilott_xchg_t* x) {
     for (int r = 0; r < (int)x->peers.size(); ++r)
         if (r != x->rank && x->peers[r]) cudaIpcCloseMemHandle(x->peers[r]);
     cudaFree(x->mine); cudaFree(x->peers_dev); cudaFree(x->err_dev); cudaFree(x->done_dev);
+    if (x->copy_stream) cudaStreamDestroy(x->copy_stream);
+    cudaFree(x->flag_vals);
+    if (x->ev_ready) cudaEventDestroy(x->ev_ready);
+    for (cudaEvent_t ev : x->ev_buf) if (ev) cudaEventDestroy(ev);
     delete x;
     return PILOTT_OK;
 }

@@ -297,7 +297,7 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_l
     // finishes last releases the step's flag on every rank (fence / counter / fence: the pattern
     // of a last-block reduction, at system scope).
     if (peers) {
-        const int slot = (int)(step & 3);
+        const int slot = (int)(step & (XCHG_SLOTS - 1));
         if (lane < k) {
             const bool ok = seq != INT64_MAX;
             const int64_t iw = ok ? seq * seq_mul + seq_add : -1;
@@ -317,7 +317,7 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_l
                 __threadfence_system();
                 for (int p = 0; p < world; ++p) {
                     uint64_t* flag = reinterpret_cast<uint64_t*>(peers[p] + flags_off) + (int64_t)slot * world + rank;
-                    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(flag), "l"((uint64_t)(step + 1)) : "memory");
+                    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(flag), "l"(PILOTT_XCHG_FLAG(step)) : "memory");
                 }
             }
         }
@@ -552,7 +552,7 @@ finish_sel_kernel(const __grid_constant__ FinishArgs a) {
         if (a.out_score64) a.out_score64[q * k + lane] = ok ? sc : -INFINITY;
     }
     if (a.peers) {                                              // row-sharded store: see finish_kernel step 4b
-        const int slot = (int)(a.step & 3);
+        const int slot = (int)(a.step & (XCHG_SLOTS - 1));
         if (lane < k) {
             const bool ok = seq != INT64_MAX;
             const int64_t iw = ok ? seq * a.seq_mul + a.seq_add : -1;
@@ -572,7 +572,7 @@ finish_sel_kernel(const __grid_constant__ FinishArgs a) {
                 __threadfence_system();
                 for (int pr = 0; pr < a.world; ++pr) {
                     uint64_t* flag = reinterpret_cast<uint64_t*>(a.peers[pr] + a.flags_off) + (int64_t)slot * a.world + a.rank;
-                    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(flag), "l"((uint64_t)(a.step + 1)) : "memory");
+                    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(flag), "l"(PILOTT_XCHG_FLAG(a.step)) : "memory");
                 }
             }
         }

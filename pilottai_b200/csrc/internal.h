@@ -99,6 +99,10 @@ cudaError_t launch_finish(const FinishArgs& a, cudaStream_t st);
 
 
 // exchange over NVLink peer memory (xchg.cu)
+// value of a slot's flag for step s: never 0 (the cleared state), exact within any window of 65536 steps
+#define PILOTT_XCHG_FLAG(step) ((uint64_t)(((step) & 0xffff) + 1))
+constexpr int XCHG_FLAG_RING = 65536;
+constexpr int XCHG_SLOTS = 8;   // steps of the exchange that may be in flight before a slot is reused (power of two)
 cudaError_t launch_xchg_publish(unsigned char* const* peers_dev, int world, int rank, int64_t block_bytes,
                                 int64_t flags_off, const void* src, int64_t bytes, int64_t step, cudaStream_t st);
 cudaError_t launch_xchg_merge(const void* mine, int world, int64_t block_bytes, int64_t flags_off, int64_t step,

@@ -1,18 +1,21 @@
 // xchg.cu -- exchange step of the row-sharded store over NVLink peer memory, without NCCL.
 //
-// Every rank owns one buffer  [4 slots][world][block_bytes]  plus  flags [4 slots][world]  and
-// has every peer's buffer mapped (CUDA IPC).  Step s uses slot s & 3.
+// Every rank owns one buffer  [8 slots][world][block_bytes]  plus  flags [8 slots][world]  and
+// has every peer's buffer mapped (CUDA IPC).  Step s uses slot s & 7.
 //   publish: one CTA per destination rank stores this rank's (index, score) block straight into
 //            the destination's buffer at [slot][my rank] with 16-byte stores over NVLink, fences
-//            at system scope and then releases flag[slot][my rank] = s + 1 there.
-//   merge:   every CTA first acquires the `world` flags of the slot (spins until each reads
-//            s + 1: all blocks have landed), then ranks the world*k candidates of its query by
+//            at system scope and then releases flag[slot][my rank] = (s mod 65536) + 1 there.
+//   merge:   a one-CTA kernel first acquires the `world` flags of the slot (spins until each reads
+//            that value: all blocks have landed), then the merge kernel ranks the world*k candidates of its query by
 //            (score desc, index asc) exactly like topk_merge_kernel.
-// Ordering rule per rank: publish(s+1) may be enqueued before merge(s) (so the exchange of one
-// batch hides behind the local search of the next and ranks may drift a step apart), but
-// publish(s+2) must follow merge(s).  Four slots are then enough: a peer overwrites my slot s & 3
-// with step s + 4 only after its own merge(s + 2), which needed my publish(s + 2), which my stream
-// ordered after my merge(s).
+//   publish by copy (abi.cu, pilott_xchg_publish_copy): the same block and flag written by the copy
+//            engines instead (cudaMemcpyAsync into each peer's buffer, then an 8-byte copy of the
+//            flag value, same stream, so in order): no SM is taken from the scan of the next batch.
+// Ordering rule per rank: up to three publishes may be enqueued ahead of the oldest outstanding
+// merge -- publish(s+1..s+3) before merge(s), so the exchange of a batch hides behind the local
+// searches that follow and ranks may drift apart -- but publish(s+4) must follow merge(s).  Eight
+// slots are then enough: a peer overwrites my slot s & 7 with step s + 8 only after its own
+// merge(s + 4), which needed my publish(s + 4), which my stream ordered after my merge(s).
 // The spin is bounded (2 s of %globaltimer): a missing peer sets an error word and the merge
 // writes "no result" rows instead of hanging the GPU.
 #include "common.cuh"
@@ -39,7 +42,7 @@ __global__ void __launch_bounds__(512)
 xchg_publish_kernel(unsigned char* const* __restrict__ peers, int world, int rank, int64_t block_bytes,
                     int64_t flags_off, const uint4* __restrict__ src, int64_t bytes, int64_t step) {
     const int dst = blockIdx.x;
-    const int slot = (int)(step & 3);
+    const int slot = (int)(step & (XCHG_SLOTS - 1));
     unsigned char* base = peers[dst];
     uint4* out = reinterpret_cast<uint4*>(base + ((int64_t)slot * world + rank) * block_bytes);
     const int64_t n16 = bytes / 16;
@@ -48,7 +51,27 @@ xchg_publish_kernel(unsigned char* const* __restrict__ peers, int world, int ran
     if (threadIdx.x == 0) {
         __threadfence_system();                        // one cumulative fence, then the release
         uint64_t* flag = reinterpret_cast<uint64_t*>(base + flags_off) + (int64_t)slot * world + rank;
-        st_release_sys(flag, (uint64_t)(step + 1));
+        st_release_sys(flag, PILOTT_XCHG_FLAG(step));
+    }
+}
+
+// The wait itself: ONE small CTA spins until every rank's flag of the slot reads this step's value
+// (bounded: 2 s, then the error word).  It is a kernel of its own so that a rank that runs ahead of
+// its peers parks a single CTA -- a thousand spinning merge CTAs would take every thread slot of the
+// GPU, and with them the slots the rank's own outgoing copies and searches need: two ranks waiting
+// for each other that way never finish.
+__global__ void __launch_bounds__(64)
+xchg_wait_kernel(const unsigned char* __restrict__ mine, int world, int64_t flags_off, int64_t step,
+                 int32_t* __restrict__ err_word) {
+    const int slot = (int)(step & (XCHG_SLOTS - 1));
+    for (int r = threadIdx.x; r < world; r += blockDim.x) {
+        const uint64_t* flag = reinterpret_cast<const uint64_t*>(mine + flags_off) + (int64_t)slot * world + r;
+        const uint64_t want = PILOTT_XCHG_FLAG(step);
+        const uint64_t t0 = globaltimer_ns();
+        while (ld_acquire_sys(flag) != want) {
+            __nanosleep(200);
+            if (globaltimer_ns() - t0 > 2000000000ull) { atomicExch(err_word, 1); break; }
+        }
     }
 }
 
@@ -61,18 +84,13 @@ xchg_merge_kernel(const unsigned char* __restrict__ mine, int world, int64_t blo
     const int total = world * k;
     double* s_sc = reinterpret_cast<double*>(sm_raw);
     int64_t* s_idx = reinterpret_cast<int64_t*>(s_sc + total);
-    const int slot = (int)(step & 3);
+    const int slot = (int)(step & (XCHG_SLOTS - 1));
     const int64_t q = blockIdx.x;
     if (threadIdx.x == 0) s_ok = 1;
     __syncthreads();
-    if (threadIdx.x < world) {                          // one thread per peer flag
+    if (threadIdx.x < world) {                          // one thread per peer flag; xchg_wait_kernel has already waited
         const uint64_t* flag = reinterpret_cast<const uint64_t*>(mine + flags_off) + (int64_t)slot * world + threadIdx.x;
-        const uint64_t want = (uint64_t)(step + 1);
-        const uint64_t t0 = globaltimer_ns();
-        while (ld_acquire_sys(flag) != want) {
-            __nanosleep(200);
-            if (globaltimer_ns() - t0 > 2000000000ull) { s_ok = 0; atomicExch(err_word, 1); break; }
-        }
+        if (ld_acquire_sys(flag) != PILOTT_XCHG_FLAG(step)) { s_ok = 0; atomicExch(err_word, 1); }
     }
     __syncthreads();
     const bool ok = s_ok != 0;
@@ -119,6 +137,9 @@ cudaError_t launch_xchg_merge(const void* mine, int world, int64_t block_bytes, 
                               int64_t nq, int k, int64_t* out_idx, float* out_score, double* out_score64,
                               int32_t* err_word, cudaStream_t st) {
     if (nq <= 0) return cudaSuccess;
+    xchg_wait_kernel<<<1, 64, 0, st>>>((const unsigned char*)mine, world, flags_off, step, err_word);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
     xchg_merge_kernel<<<(unsigned)nq, 256, (size_t)world * k * 16, st>>>((const unsigned char*)mine, world, block_bytes,
                                                                         flags_off, step, nq, k, out_idx, out_score,
                                                                         out_score64, err_word);

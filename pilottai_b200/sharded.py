@@ -8,18 +8,26 @@ i // world (round-robin keeps streaming inserts and ring eviction balanced).  A 
 which is identical to what one store holding every row returns.  There is no reference
 counterpart: the reference is single-process.
 
-Two exchanges:
-  "nccl" (default) -- one all_gather_into_tensor of the packed block on NCCL's own stream +
-         pilott_topk_merge_packed; with two slots the exchange of batch i overlaps the local search
-         of batch i+1 and nothing but the merge kernel sits on the search stream.
+Three exchanges:
+  "copy" (default) -- pilott_xchg_publish_copy: the block and a flag are written into every peer's mapped
+         receive buffer by the copy engines (cudaMemcpyAsync on a side stream), the merge kernel
+         acquires the flags.  No kernel runs for the exchange, so nothing competes with the scan of
+         the next batch for SMs: on B200 the pair scan occupies all 72 SM pairs, and a single CTA
+         of a collective's kernel on the wrong SM holds one pair back for the length of the
+         collective.  Measured on 8 B200, 1 M x 768, 1024-query batches, 0.177 ms of local search
+         per step: 0.194 ms per step with this exchange, 0.230 with the NCCL one below.
+         If peer mapping fails on any rank, every rank falls back to "nccl".
+  "nccl" -- one all_gather_into_tensor of the packed block on NCCL's own stream (a process group
+         of its own, held to one CTA) + pilott_topk_merge_packed; the exchange of batch i overlaps
+         the local searches of the batches behind it.
   "p2p"  -- pilott_xchg_*: every rank maps every peer's receive buffer (CUDA IPC);
          finish_kernel stores each result row straight into the peers over NVLink and the last
          CTA releases a flag, the merge kernel acquires the flags and ranks.  No collective
          library on the data path.  Measured on 8 B200 (1 M x 768, 1024-query batches) it is the
-         slower of the two for this 160 KB payload: 0.254 ms per step against 0.231 ms, because the
-         remote stores, the system-scope fence and the flag acquire all sit on the search stream
-         while NCCL's copy runs beside it.  Select it with exchange="p2p" or PILOTT_EXCHANGE=p2p;
-         if peer mapping fails on any rank, every rank falls back to "nccl".
+         slowest of the three for this 160 KB payload (round 1: 0.254 ms per step): the remote stores,
+         the system-scope fence and the flag release sit inside the finish kernel on the search stream.
+  Select with exchange= or PILOTT_EXCHANGE=copy|nccl|p2p.  Whatever the exchange, the merge kernel
+  runs on a side stream (search_end).
 """
 from __future__ import annotations
 
@@ -48,12 +56,12 @@ class ShardedSemanticStore:
     def __init__(self, dim: int, capacity: int, rank: int, world: int, device: int,
                  group: Optional[dist.ProcessGroup] = None, exchange: str = "auto"):
         self.rank, self.world, self.group = rank, world, group
-        if group is None and world > 1 and exchange != "p2p" and os.environ.get("PILOTT_EXCHANGE", "nccl") != "p2p":
+        if group is None and world > 1 and (exchange == "nccl" or (exchange == "auto" and os.environ.get("PILOTT_EXCHANGE", "copy") == "nccl")):
             self.group = self._small_nccl_group(world)
         if exchange == "auto":
-            exchange = os.environ.get("PILOTT_EXCHANGE", "nccl")
-        if exchange not in ("p2p", "nccl"):
-            raise ValueError("exchange must be 'auto', 'p2p' or 'nccl'")
+            exchange = os.environ.get("PILOTT_EXCHANGE", "copy")
+        if exchange not in ("p2p", "nccl", "copy"):
+            raise ValueError("exchange must be 'auto', 'copy', 'p2p' or 'nccl'")
         self.exchange = exchange if world > 1 else "none"
         self._xchg = {}                                 # (nq, k) -> [handle, next step]
         self._ridx = {}                                 # cached row-selection indices for device appends
@@ -66,6 +74,7 @@ class ShardedSemanticStore:
         self.dim, self.device = dim, device
         self.total = 0                                  # global rows ever appended
         self._bufs = {}
+        self._merge_stream = None
 
     @staticmethod
     def _small_nccl_group(world: int):
@@ -123,6 +132,7 @@ class ShardedSemanticStore:
                 "m_idx": pack[:ib].view(torch.int64).view(nq, k),
                 "m_sc": pack[ib: ib + sb].view(torch.float32).view(nq, k),
                 "m_sc64": torch.empty((nq, k), dtype=torch.float64, device=dev),
+                "begun": torch.cuda.Event(), "merged": torch.cuda.Event(), "merge_pending": False,
             }
         return self._bufs[key]
 
@@ -147,6 +157,8 @@ class ShardedSemanticStore:
             if rc == 0:
                 lib.pilott_xchg_destroy(x)
             self.exchange = "nccl"
+            if self.group is None:                   # (collective: every rank takes this branch together)
+                self.group = self._small_nccl_group(self.world)
             return None
         self._xchg[key] = [x, 0]
         return self._xchg[key]
@@ -155,20 +167,28 @@ class ShardedSemanticStore:
         """Local search, then the block is sent on its way (publish kernel over NVLink, or ONE
         asynchronous all-gather).  Returns a ticket for search_end(), which merges.  With two
         buffer slots a caller overlaps the exchange of batch i with the local search of batch i+1
-        (at most ONE search_begin ahead of the matching search_end: the exchange has 4 slots).
+        (at most THREE search_begin ahead of the oldest outstanding search_end with the "copy" and "p2p"
+        exchanges -- their buffers have 8 slots, see csrc/xchg.cu -- and with distinct `slot`s).
         resolve=True reads the local inexact counter (one host sync) and repairs flagged queries
         before the exchange.  With resolve=False flagged rows are exchanged as they are, and every
         rank only sees its OWN counter: sum `self.local.flagged_total()` over the ranks (one
         all-reduce, at any later point -- the library counts across searches) before trusting the
         merged results, as bench.py does."""
         b = self._buffers(q.shape[0], k, q.device, slot)
-        xs = self._exchange_for(q.shape[0], k) if self.exchange == "p2p" else None
+        if b.get("merge_pending"):                        # this slot's previous merge may still read its blocks
+            torch.cuda.current_stream(self.device).wait_event(b["merged"])
+            b["merge_pending"] = False
+        xs = self._exchange_for(q.shape[0], k) if self.exchange in ("p2p", "copy") else None
+        by_copy = xs is not None and self.exchange == "copy"
+        if by_copy:                                       # the copy engines may still be reading this slot's block
+            check(_lib.load().pilott_xchg_wait_buffer(xs[0], slot % 8, self.local._stream()))
         large = k > _lib.MAX_FUSED_K                      # local top-k through the threshold-collect path (exact, synchronous)
-        if xs is not None and not resolve and not large:
+        if xs is not None and not resolve and not large and not by_copy:
             # fused: finish_kernel stores the result rows into every rank's buffer as it produces them
             step = xs[1]
             xs[1] += 1
             self.local.search_publish_into(xs[0], step, q, k, b["idx"], b["sc"], b["sc64"], b["inexact"], b["flags"], **flt)
+            b["begun"].record(torch.cuda.current_stream(self.device))
             return b, ("p2p", xs[0], step, q.shape[0], k)
         if large:
             self.local.search_large(q, k, out=(b["idx"], b["sc"], b["sc64"]), **flt)
@@ -179,26 +199,48 @@ class ShardedSemanticStore:
             self.local.refine(q, k, b["flags"].nonzero(), (b["idx"], b["sc"], b["sc64"]), **flt)
             b["inexact"].zero_()
         work = None
-        if xs is not None:                               # repaired rows: publish the block with its own kernel
+        if xs is not None:                               # the block goes out by copy engine, or (repaired rows) by the publish kernel
             step = xs[1]
             xs[1] += 1
-            check(_lib.load().pilott_xchg_publish(xs[0], ptr(b["mine"]), b["mine"].numel() * 8, step, self.local._stream()))
+            if by_copy:
+                check(_lib.load().pilott_xchg_publish_copy(xs[0], ptr(b["mine"]), b["mine"].numel() * 8, step, slot % 8,
+                                                           self.local._stream()))
+            else:
+                check(_lib.load().pilott_xchg_publish(xs[0], ptr(b["mine"]), b["mine"].numel() * 8, step, self.local._stream()))
+            b["begun"].record(torch.cuda.current_stream(self.device))
             return b, ("p2p", xs[0], step, q.shape[0], k)
         if self.world > 1:
             work = dist.all_gather_into_tensor(b["gathered"], b["mine"], group=self.group, async_op=True)
+            b["begun"].record(torch.cuda.current_stream(self.device))
         return b, work
 
-    def search_end(self, ticket):
+    def search_end(self, ticket, wait: bool = True):
+        """Merges the exchanged blocks of one search_begin.  The merge kernel runs on a side stream of
+        the store: it is small enough to sit beside the scan of a later batch on the same SMs, so it
+        costs the search stream nothing.  wait=True (default) makes the CURRENT stream wait for it, so
+        the returned tensors can be used like any other; wait=False returns at once and leaves the
+        ordering to the caller (`ticket[0]["merged"]` is the torch event to wait for) -- what a
+        pipeline does that only hands the results to a copy stream."""
         b, work = ticket
         if self.world == 1:
             return b["idx"], b["sc"], b["sc64"], b["inexact"]
-        if isinstance(work, tuple):                      # peer-memory exchange: the block is already on its way
-            _, x, step, nq, k = work
-            check(_lib.load().pilott_xchg_merge(x, step, nq, k, ptr(b["m_idx"]), ptr(b["m_sc"]), ptr(b["m_sc64"]),
-                                                self.local._stream()))
-        else:
-            work.wait()
-            topk_merge_packed(b["gathered"], out=(b["m_idx"], b["m_sc"], b["m_sc64"]))
+        main = torch.cuda.current_stream(self.device)
+        if self._merge_stream is None:
+            self._merge_stream = torch.cuda.Stream(device=self.device)
+        self._merge_stream.wait_event(b["begun"])        # recorded by search_begin behind its local search / publish
+        with torch.cuda.stream(self._merge_stream):
+            if isinstance(work, tuple):                  # peer-memory exchange: the block is already on its way
+                _, x, step, nq, k = work
+                check(_lib.load().pilott_xchg_merge(x, step, nq, k, ptr(b["m_idx"]), ptr(b["m_sc"]), ptr(b["m_sc64"]),
+                                                    self.local._stream()))
+            else:
+                work.wait()
+                topk_merge_packed(b["gathered"], out=(b["m_idx"], b["m_sc"], b["m_sc64"]))
+            b["merged"].record(self._merge_stream)
+        b["merge_pending"] = True
+        if wait:
+            main.wait_event(b["merged"])
+            b["merge_pending"] = False
         return b["m_idx"], b["m_sc"], b["m_sc64"], b["inexact"]
 
     def check_exchange(self) -> None:

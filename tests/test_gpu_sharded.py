@@ -90,7 +90,7 @@ def _worker(rank, world, port, n, dim, nq, k, out, exchange):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("exchange", ["p2p", "nccl"])
+@pytest.mark.parametrize("exchange", ["copy", "p2p", "nccl"])
 def test_sharded_search_equals_single_store(torch_cuda, tmp_path, exchange):
     torch = torch_cuda
     world = min(torch.cuda.device_count(), 4)

@@ -45,7 +45,7 @@ def run(st, nslot, local_only=False):
             return
         pending.append(st.search_begin(qpool[i % 8], K, slot=i % nslot))
         if len(pending) >= nslot:
-            st.search_end(pending.pop(0))
+            st.search_end(pending.pop(0), wait=False)
 
     for i in range(10):
         step(i)
@@ -71,14 +71,29 @@ def run(st, nslot, local_only=False):
 
 
 # (the peer-memory exchange allows ONE search_begin ahead of its search_end: two slots only)
-variants = [("nccl", "2", 2), ("nccl", "2", 4), ("nccl", "1", 2), ("nccl", "0", 2), ("p2p", "0", 2)] if world > 1 else [("nccl", "0", 2)]
-for exchange, ctas, nslot in variants:
+variants = [("copy", "1", 4, 0), ("copy", "1", 2, 0), ("nccl", "1", 4, 0), ("nccl", "1", 4, 140), ("p2p", "1", 2, 0)] if world > 1 else [("nccl", "0", 2, 0)]
+if len(sys.argv) > 4:
+    variants = [v for v in variants if v[0] in sys.argv[4].split(",")]
+for exchange, ctas, nslot, scan_ctas in variants:
     os.environ["PILOTT_NCCL_MAX_CTAS"] = ctas
     st = build(exchange)
+    if scan_ctas:
+        st.local.set_ctas(scan_ctas)
+    # a broken exchange must not cost 2 s per step: three steps first, then ask
+    tk = [st.search_begin(qpool[i], K, slot=i) for i in range(2)]
+    for t in tk:
+        st.search_end(t)
+    try:
+        st.check_exchange()
+    except Exception as e:
+        if rank == 0:
+            print(f"world {world} exchange {exchange}: BROKEN ({e}), skipped", flush=True)
+        st.close()
+        continue
     for label, kw in (("local search only", dict(nslot=2, local_only=True)), (f"{nslot} slots", dict(nslot=nslot))):
         d, h = run(st, **kw)
         if rank == 0:
-            print(f"world {world} rows {rows} pdl={os.environ.get('PILOTT_PDL', '1')} exchange {st.exchange:5s} max_ctas {ctas} {label:18s}: device {d:.4f} ms/step, host enqueue {h:.4f} ms/step", flush=True)
+            print(f"world {world} rows {rows} exchange {st.exchange:5s} nccl_ctas {ctas} scan_ctas {scan_ctas or 'all'} {label:18s}: device {d:.4f} ms/step, host enqueue {h:.4f} ms/step", flush=True)
     st.close()
 if world > 1:
     dist.destroy_process_group()
