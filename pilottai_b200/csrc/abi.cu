@@ -1381,7 +1381,11 @@ int pilott_xchg_wait_buffer(pilott_xchg_t* x, int buffer_id, void* stream) {
     if (!x) return fail(PILOTT_EINVAL, "NULL pointer");
     if (buffer_id < 0 || buffer_id >= 8) return fail(PILOTT_EINVAL, "buffer_id must be in [0, 8)");
     DeviceGuard g(x->device);
-    CK(cudaStreamWaitEvent((cudaStream_t)stream, x->ev_buf[buffer_id], 0));      // a never-recorded event is complete
+    // (a never-recorded event is complete; one that has completed needs no wait in the stream, and a
+    //  wait between two kernels would cost them their programmatic overlap)
+    const cudaError_t q = cudaEventQuery(x->ev_buf[buffer_id]);
+    if (q == cudaErrorNotReady) CK(cudaStreamWaitEvent((cudaStream_t)stream, x->ev_buf[buffer_id], 0));
+    else if (q != cudaSuccess) return fail_cuda(q, "cudaEventQuery(copy done)");
     return PILOTT_OK;
 }
 

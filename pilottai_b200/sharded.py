@@ -176,7 +176,8 @@ class ShardedSemanticStore:
         merged results, as bench.py does."""
         b = self._buffers(q.shape[0], k, q.device, slot)
         if b.get("merge_pending"):                        # this slot's previous merge may still read its blocks
-            torch.cuda.current_stream(self.device).wait_event(b["merged"])
+            if not b["merged"].query():                   # (normally long done: no wait, and the launches stay back to back)
+                torch.cuda.current_stream(self.device).wait_event(b["merged"])
             b["merge_pending"] = False
         xs = self._exchange_for(q.shape[0], k) if self.exchange in ("p2p", "copy") else None
         by_copy = xs is not None and self.exchange == "copy"
