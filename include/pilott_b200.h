@@ -322,6 +322,22 @@ int pilott_route_score(const uint64_t* task_req_dev, const uint64_t* task_tags_d
                        const double* spec_u_dev, int max_tags, int mode, int32_t* out_agent_dev,
                        double* out_score_dev, void* stream);
 
+/* The same scoring with the task x agent matching on the tcgen05 tensor cores (csrc/route_tc.cu):
+ * the bit sets are expanded into two bf16 feature matrices inside `workspace_dev`, ONE GEMM yields,
+ * per (task, agent), the packed counts {required capabilities held, attribute missing, type match,
+ * tag matches} as an exact fp32 integer, and the epilogue that reads TMEM assembles the score and
+ * keeps the first maximum.  Same arguments, same outputs, bit-identical results.  Takes
+ * words <= 3 and agent tables of up to about 1500 agents (PILOTT_EUNSUPPORTED otherwise: use
+ * pilott_route_score); workspace_bytes >= pilott_route_tc_workspace(nt, na, words). */
+int64_t pilott_route_tc_workspace(int64_t nt, int na, int words);
+int pilott_route_score_tc(const uint64_t* task_req_dev, const uint64_t* task_tags_dev,
+                          const int32_t* task_type_dev, const uint8_t* task_flags_dev, int64_t nt,
+                          const uint64_t* agent_caps_dev, const uint64_t* agent_spec_dev,
+                          const uint8_t* agent_flags_dev, const double* agent_s12_dev,
+                          const double* agent_t4_dev, int na, int words, const double* spec_u_dev,
+                          int max_tags, int mode, int32_t* out_agent_dev, double* out_score_dev,
+                          void* workspace_dev, int64_t workspace_bytes, void* stream);
+
 /* TaskRouter.get_task_priority (pilott/core/router.py:135-145) for nt tasks:
  * 3 critical, 2 high, 1 medium, 0 low. */
 int pilott_task_priority(const uint8_t* urgent_dev, const int32_t* complexity_dev,

@@ -64,6 +64,9 @@ SIGNATURES = {
     "pilott_topk_merge_packed": (C.c_int, [c_vp, C.c_int, c_i64, C.c_int, c_vp, c_vp, c_vp, c_vp]),
     "pilott_route_score": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, C.c_int,
                                      C.c_int, c_vp, C.c_int, C.c_int, c_vp, c_vp, c_vp]),
+    "pilott_route_tc_workspace": (c_i64, [c_i64, C.c_int, C.c_int]),
+    "pilott_route_score_tc": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, C.c_int,
+                                        C.c_int, c_vp, C.c_int, C.c_int, c_vp, c_vp, c_vp, c_i64, c_vp]),
     "pilott_task_priority": (C.c_int, [c_vp, c_vp, c_vp, c_i64, c_vp, c_vp]),
 }
 

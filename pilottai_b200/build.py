@@ -15,8 +15,8 @@ OUT = os.path.join(HERE, "libpilott_b200.so")
 # host-side helper (CPython extension, plain C): task dicts -> routing kernel columns
 TASKENC_SRC = os.path.join(CSRC, "task_encode.c")
 TASKENC_OUT = os.path.join(HERE, "_taskenc" + (__import__("sysconfig").get_config_var("EXT_SUFFIX") or ".so"))
-SOURCES = ["abi.cu", "store_kernels.cu", "scan_generic.cu", "scan_tc.cu", "finish.cu", "route.cu", "xchg.cu"]
-HEADERS = ["common.cuh", "internal.h", os.path.join("..", "..", "include", "pilott_b200.h")]
+SOURCES = ["abi.cu", "store_kernels.cu", "scan_generic.cu", "scan_tc.cu", "finish.cu", "route.cu", "route_tc.cu", "xchg.cu"]
+HEADERS = ["common.cuh", "internal.h", "tc_ptx.cuh", os.path.join("..", "..", "include", "pilott_b200.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC",

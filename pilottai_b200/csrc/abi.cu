@@ -1448,6 +1448,40 @@ int pilott_route_score(const uint64_t* task_req_dev, const uint64_t* task_tags_d
     return PILOTT_OK;
 }
 
+int64_t pilott_route_tc_workspace(int64_t nt, int na, int words) {
+    if (nt < 0 || na < 0 || words < 1) return 0;
+    return pilott::route_tc_workspace_bytes(nt, na, words);
+}
+
+int pilott_route_score_tc(const uint64_t* task_req_dev, const uint64_t* task_tags_dev, const int32_t* task_type_dev,
+                          const uint8_t* task_flags_dev, int64_t nt, const uint64_t* agent_caps_dev,
+                          const uint64_t* agent_spec_dev, const uint8_t* agent_flags_dev,
+                          const double* agent_s12_dev, const double* agent_t4_dev, int na, int words,
+                          const double* spec_u_dev, int max_tags, int mode, int32_t* out_agent_dev,
+                          double* out_score_dev, void* workspace_dev, int64_t workspace_bytes, void* stream) {
+    if (nt < 0 || na < 0) return fail(PILOTT_EINVAL, "negative size");
+    if (max_tags < 64 * words) return fail(PILOTT_EINVAL, "max_tags must be >= 64*words");
+    if (mode < 0 || mode > 2) return fail(PILOTT_EINVAL, "mode must be 0, 1 or 2");
+    if (nt == 0) return PILOTT_OK;
+    if (!pilott::route_tc_supported(na, words, max_tags))
+        return fail(PILOTT_EUNSUPPORTED, "tensor-core routing takes 1..3 mask words and an agent table that fits shared memory "
+                                         "(about 1500 agents): use pilott_route_score");
+    if (!task_req_dev || !task_tags_dev || !task_type_dev || !task_flags_dev || !out_agent_dev || !out_score_dev ||
+        !agent_caps_dev || !agent_spec_dev || !agent_flags_dev || !agent_s12_dev || !agent_t4_dev || !spec_u_dev)
+        return fail(PILOTT_EINVAL, "NULL pointer");
+    if (!workspace_dev || workspace_bytes < pilott::route_tc_workspace_bytes(nt, na, words))
+        return fail(PILOTT_EINVAL, "workspace is smaller than pilott_route_tc_workspace(nt, na, words)");
+    int dev = 0, sms = 0;
+    CK(cudaGetDevice(&dev));
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    int rc = get_encode();
+    if (rc) return rc;
+    CK(pilott::launch_route_tc(task_req_dev, task_tags_dev, task_type_dev, task_flags_dev, nt, agent_caps_dev, agent_spec_dev,
+                               agent_flags_dev, agent_s12_dev, agent_t4_dev, na, words, spec_u_dev, max_tags, mode,
+                               out_agent_dev, out_score_dev, workspace_dev, sms, &encode_map, (cudaStream_t)stream));
+    return PILOTT_OK;
+}
+
 int pilott_task_priority(const uint8_t* urgent_dev, const int32_t* complexity_dev, const int32_t* n_deps_dev,
                          int64_t nt, uint8_t* out_dev, void* stream) {
     if (nt < 0) return fail(PILOTT_EINVAL, "negative size");

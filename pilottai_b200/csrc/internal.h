@@ -149,6 +149,15 @@ cudaError_t launch_route(const uint64_t* task_req, const uint64_t* task_tags,
                          const double* agent_s12, const double* agent_t4, int na, int words,
                          const double* spec_u, int max_tags, int mode, int32_t* out_agent,
                          double* out_score, cudaStream_t st);
+// tcgen05 form of the same scoring (route_tc.cu): bit sets -> bf16 feature matrices in `workspace` -> GEMM + epilogue
+int64_t route_tc_workspace_bytes(int64_t nt, int na, int words);
+bool route_tc_supported(int na, int words, int max_tags);
+cudaError_t launch_route_tc(const uint64_t* task_req, const uint64_t* task_tags, const int32_t* task_type,
+                            const uint8_t* task_flags, int64_t nt, const uint64_t* agent_caps, const uint64_t* agent_spec,
+                            const uint8_t* agent_flags, const double* agent_s12, const double* agent_t4, int na, int words,
+                            const double* spec_u, int max_tags, int mode, int32_t* out_agent, double* out_score,
+                            void* workspace, int num_sms, int (*encode)(CUtensorMap*, const void*, int64_t, int, int),
+                            cudaStream_t st);
 cudaError_t launch_task_priority(const uint8_t* urgent, const int32_t* complexity,
                                  const int32_t* ndeps, int64_t nt, uint8_t* out, cudaStream_t st);
 

@@ -30,6 +30,9 @@ from . import _lib
 from ._lib import check, ptr
 
 MODE = {"router": 0, "load_balancer": 1, "delegator": 2}
+# kernel="auto": which form of K5 runs (set from the measurements in DESIGN.md K5)
+AUTO_TC = False
+AUTO_TC_MIN_TASKS = 65536
 PRIORITY_NAMES = ["low", "medium", "high", "critical"]
 
 
@@ -243,6 +246,7 @@ class RoutingEngine:
                                                else np.ascontiguousarray(arr)).to(self.device)
         self.d_caps, self.d_spec, self.d_u = self._d(caps), self._d(spec), self._d(u)
         self._tables: Dict[tuple, tuple] = {}
+        self._ws = None                      # workspace of the tensor-core form (bf16 feature matrices)
 
     def _table(self, mode: str, **cfg):
         key = (mode, tuple(sorted((k, repr(v)) for k, v in cfg.items() if k != "lb_metrics")), id(cfg.get("lb_metrics")))
@@ -274,9 +278,12 @@ class RoutingEngine:
         self._tables[key] = tab
         return tab
 
-    def route_encoded(self, enc: Dict[str, "np.ndarray"], mode: str = "router", **cfg):
+    def route_encoded(self, enc: Dict[str, "np.ndarray"], mode: str = "router", kernel: str = "auto", **cfg):
         """enc: arrays from encode_tasks (numpy) or the same keys as CUDA tensors.
-        Returns (agent index int32 [T] (-1 = none), score fp64 [T]) as CUDA tensors."""
+        Returns (agent index int32 [T] (-1 = none), score fp64 [T]) as CUDA tensors.
+        kernel: "cuda" = route_kernel (set arithmetic on CUDA cores, any vocabulary width), "tc" = the
+        tcgen05 GEMM form (pilott_route_score_tc: up to 192-bit vocabularies), "auto" = the faster of
+        the two as measured on B200.  Same results from both, bit for bit."""
         torch = self._torch
         d_s12, d_t4, d_flags, d_caps, d_spec, d_keep = self._table(mode, **cfg)
         t = {k: (self._d(v) if isinstance(v, np.ndarray) else v) for k, v in enc.items()}
@@ -284,10 +291,22 @@ class RoutingEngine:
         out_a = torch.empty(nt, dtype=torch.int32, device=self.device)
         out_s = torch.empty(nt, dtype=torch.float64, device=self.device)
         st = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
-        check(self._lib.pilott_route_score(ptr(t["req"]), ptr(t["tags"]), ptr(t["type"]), ptr(t["flags"]), nt,
-                                           ptr(d_caps), ptr(d_spec), ptr(d_flags), ptr(d_s12), ptr(d_t4),
-                                           int(d_keep.numel()), self.vocab.words, ptr(self.d_u), self.max_tags,
-                                           MODE[mode], ptr(out_a), ptr(out_s), st))
+        na = int(d_keep.numel())
+        if kernel == "auto":
+            kernel = "tc" if (AUTO_TC and self.vocab.words <= 3 and 0 < na <= 1280 and nt >= AUTO_TC_MIN_TASKS) else "cuda"
+        if kernel == "tc":
+            need = int(self._lib.pilott_route_tc_workspace(nt, na, self.vocab.words))
+            if self._ws is None or self._ws.numel() < need:
+                self._ws = torch.empty(need + need // 8, dtype=torch.uint8, device=self.device)
+            check(self._lib.pilott_route_score_tc(ptr(t["req"]), ptr(t["tags"]), ptr(t["type"]), ptr(t["flags"]), nt,
+                                                  ptr(d_caps), ptr(d_spec), ptr(d_flags), ptr(d_s12), ptr(d_t4), na,
+                                                  self.vocab.words, ptr(self.d_u), self.max_tags, MODE[mode], ptr(out_a),
+                                                  ptr(out_s), ptr(self._ws), self._ws.numel(), st))
+        else:
+            check(self._lib.pilott_route_score(ptr(t["req"]), ptr(t["tags"]), ptr(t["type"]), ptr(t["flags"]), nt,
+                                               ptr(d_caps), ptr(d_spec), ptr(d_flags), ptr(d_s12), ptr(d_t4),
+                                               na, self.vocab.words, ptr(self.d_u), self.max_tags,
+                                               MODE[mode], ptr(out_a), ptr(out_s), st))
         if 0 < d_keep.numel() < len(self.agents):      # map compacted positions back to table indices
             out_a = torch.where(out_a >= 0, d_keep[out_a.clamp(min=0).long()], out_a)
         return out_a, out_s
@@ -299,13 +318,13 @@ class RoutingEngine:
     def to_device(self, arr: np.ndarray):
         return self._d(arr)
 
-    def route(self, tasks: Sequence[dict], mode: str = "router", as_numpy: bool = False, **cfg):
+    def route(self, tasks: Sequence[dict], mode: str = "router", as_numpy: bool = False, kernel: str = "auto", **cfg):
         """Dict tasks -> (agent index, score) per task on the host: lists, or numpy arrays
         (int32 / fp64) with as_numpy=True -- the form a million-task batch wants."""
         if not tasks:
             return (np.empty(0, np.int32), np.empty(0, np.float64)) if as_numpy else ([], [])
         enc = self.encode(tasks)
-        a, s = self.route_encoded({k: enc[k] for k in ("req", "tags", "type", "flags")}, mode, **cfg)
+        a, s = self.route_encoded({k: enc[k] for k in ("req", "tags", "type", "flags")}, mode, kernel, **cfg)
         if as_numpy:
             return a.cpu().numpy(), s.cpu().numpy()
         return a.cpu().tolist(), s.cpu().tolist()

@@ -144,3 +144,58 @@ def test_random_tables_match_oracle_in_all_three_modes(torch_cuda, seed):
         want, ws = ro.delegator_find_best(agents, t)
         assert (agents[i]["id"] if i >= 0 else None) == want, (seed, na, extra)
         assert want is None or float(s).hex() == float(ws).hex()
+
+
+@pytest.mark.parametrize("seed", range(10))
+def test_tensor_core_form_equals_cuda_core_form(torch_cuda, seed):
+    """pilott_route_score_tc (tcgen05 GEMM of packed counts + epilogue from TMEM) against
+    pilott_route_score (set arithmetic): same agent and bit-identical fp64 score for every task, in
+    all three modes, for vocabularies of one to three mask words, agent counts around the 256-column
+    tile, agents without attributes, unknown capabilities / types / tags, tasks without keys -- and
+    both against the oracle on a sample."""
+    torch = torch_cuda
+    from pilottai_b200.routing import RoutingEngine
+    rng = np.random.default_rng(900 + seed)
+    na = int(rng.choice([1, 7, 130, 255, 256, 257, 600, 1024]))
+    extra = int(rng.choice([0, 0, 40, 100]))                      # -> 1, 2 or 3 mask words
+    agents = synth.agent_table(na, seed=seed + 30)
+    xc, xs = [f"xc{i}" for i in range(extra)], [f"xs{i}" for i in range(extra)]
+    for a in agents:
+        if a["caps"] is not None:
+            a["caps"] = a["caps"] + [c for c in xc if rng.random() < 0.4]
+        if a["specializations"] is not None:
+            a["specializations"] = a["specializations"] + [s for s in xs if rng.random() < 0.2]
+    tasks = synth.task_table(700, seed=seed + 40)
+    for t in tasks[::2]:
+        if extra and "required_capabilities" in t:
+            t["required_capabilities"] = t["required_capabilities"] + [str(c) for c in rng.choice(xc, 1)]
+        if extra and rng.random() < 0.5:
+            t["type"] = str(rng.choice(xs))
+    eng = RoutingEngine(agents, 0)
+    assert eng.vocab.words <= 3
+    thr = float(rng.choice([0.5, 0.8, 1.0]))
+    lbm = {a["id"]: ro.lb_metrics(a, 10.0, 20.0) for a in agents}
+    for mode, cfg in (("router", dict(load_threshold=thr)),
+                      ("load_balancer", dict(lb_metrics=lbm, max_tasks_per_agent=60, overload_threshold=thr)),
+                      ("delegator", {})):
+        a1, s1 = eng.route(tasks, mode, as_numpy=True, kernel="cuda", **cfg)
+        a2, s2 = eng.route(tasks, mode, as_numpy=True, kernel="tc", **cfg)
+        assert np.array_equal(a1, a2), (seed, mode, na, extra, np.nonzero(a1 != a2)[0][:5])
+        assert np.array_equal(s1.view(np.int64), s2.view(np.int64)), (seed, mode)
+    for t in range(0, 700, 35):
+        want, ws = ro.router_route(agents, tasks[t], thr)
+        a2, s2 = eng.route(tasks[t:t + 1], "router", as_numpy=True, kernel="tc", load_threshold=thr)
+        assert (agents[a2[0]]["id"] if a2[0] >= 0 else None) == want
+        assert want is None or float(s2[0]).hex() == float(ws).hex()
+
+
+def test_tensor_core_form_on_reference_fixtures(torch_cuda, golden_dir):
+    from pilottai_b200.routing import RoutingEngine
+    with open(os.path.join(golden_dir, "routing_mid.json")) as f:
+        g = json.load(f)
+    eng = RoutingEngine(g["agents"], 0)
+    idx, sc = eng.route(g["tasks"], "router", kernel="tc", load_threshold=g["load_threshold"])
+    assert [g["agents"][i]["id"] if i >= 0 else None for i in idx] == [r["agent"] for r in g["router"]]
+    for s, r in zip(sc, g["router"]):
+        if r["agent"] is not None:
+            assert float(s).hex() == r["score"]
