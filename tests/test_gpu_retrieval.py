@@ -200,8 +200,8 @@ def test_search_medium_matches_oracle(torch_cuda, kernel):
 
 def test_full_size_properties(torch_cuda):
     """BASELINE.json config 2 shape (1M x 768, 1024 queries, top-10): the tcgen05 kernels
-    must agree with the generic CUDA-core kernel on every query, a sample of queries must
-    match the CPU oracle bit for bit, and planted duplicates of the queries must come back
+    must agree with the generic CUDA-core kernel on every query, a quarter of the queries (256)
+    must match the CPU oracle bit for bit, and planted duplicates of the queries must come back
     first with score 1.0."""
     torch = torch_cuda
     n, dim, nq = 1_000_000, 768, 1024
@@ -224,8 +224,10 @@ def test_full_size_properties(torch_cuda):
     idx, sc, sc64 = res["tc"]
     assert np.array_equal(idx[:64, 0], plant) and np.all(sc[:64, 0] == 1.0)
     assert np.all(np.diff(sc64, axis=1) <= 0)                      # sorted
-    sample = [0, 63, 64, 500, 1023]
-    oidx, osc = retrieval_c.search(os_, q[sample], 10)
+    # every fourth query (256 of the 1024) against the oracle over all 1M rows, bit for bit
+    # (row-range form of the C twin: one pass over the corpus scores all sampled queries)
+    sample = np.arange(0, nq, 4)
+    oidx, osc = retrieval_c.search_rows(os_, q[sample], 10)
     assert np.array_equal(idx[sample], oidx) and np.array_equal(sc64[sample], osc)
     gs.close()
 
