@@ -270,6 +270,20 @@ int pilott_mem_search_publish(pilott_mem_t* h, pilott_xchg_t* x, int64_t step, c
                               int k, int32_t min_prio, uint64_t req_tagmask, int64_t now_us,
                               int64_t* out_idx_dev, float* out_score_dev, double* out_score64_dev,
                               int32_t* out_inexact_dev, uint8_t* out_flags_dev, void* stream);
+/* The whole sharded search in one call, for hosts that do not pipeline: local fused search of this
+ * rank's rows (global indices: options 5 / 6 of the store) into block_dev ([2][nq][k] 64-bit words,
+ * caller-owned, one per step in flight), publish by copy, wait for every rank's block of `step`,
+ * merge into out_idx / out_score / out_score64 [nq, k] -- all enqueued on `stream`, nothing
+ * synchronises.  Every rank calls it with the same step, queries and filters; the result is what
+ * one store holding every row returns (1 <= k <= PILOTT_MAX_FUSED_K; *out_inexact_dev counts this
+ * rank's flagged queries: sum pilott_mem_flagged_total over the ranks before trusting the rows, or
+ * repair with pilott_mem_search_refine and the split calls).  This is the role of the
+ * pilott_shard_init / pilott_mem_search_sharded pair SURVEY.md section 8(b) planned over
+ * ncclComm_t; the exchange it rides on needs no collective library.  No reference counterpart. */
+int pilott_mem_search_sharded(pilott_mem_t* h, pilott_xchg_t* x, int64_t step, const float* q_dev, int64_t nq,
+                              int k, int32_t min_prio, uint64_t req_tagmask, int64_t now_us,
+                              int64_t* out_idx_dev, float* out_score_dev, double* out_score64_dev,
+                              int32_t* out_inexact_dev, uint8_t* out_flags_dev, void* block_dev, void* stream);
 int pilott_xchg_check(pilott_xchg_t* x);
 int pilott_xchg_destroy(pilott_xchg_t* x);
 

@@ -58,6 +58,8 @@ SIGNATURES = {
     "pilott_xchg_merge": (C.c_int, [c_vp, c_i64, c_i64, C.c_int, c_vp, c_vp, c_vp, c_vp]),
     "pilott_mem_search_publish": (C.c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, C.c_int, c_i32, c_u64, c_i64, c_vp, c_vp,
                                             c_vp, c_vp, c_vp, c_vp]),
+    "pilott_mem_search_sharded": (C.c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, C.c_int, c_i32, c_u64, c_i64, c_vp, c_vp,
+                                            c_vp, c_vp, c_vp, c_vp, c_vp]),
     "pilott_xchg_check": (C.c_int, [c_vp]),
     "pilott_xchg_destroy": (C.c_int, [c_vp]),
     "pilott_topk_merge": (C.c_int, [c_vp, c_vp, C.c_int, c_i64, C.c_int, c_vp, c_vp, c_vp, c_vp]),

@@ -1403,6 +1403,35 @@ int pilott_xchg_merge(pilott_xchg_t* x, int64_t step, int64_t nq, int k, int64_t
     return PILOTT_OK;
 }
 
+int pilott_mem_search_sharded(pilott_mem_t* h, pilott_xchg_t* x, int64_t step, const float* q_dev, int64_t nq, int k,
+                              int32_t min_prio, uint64_t req_tagmask, int64_t now_us, int64_t* out_idx_dev,
+                              float* out_score_dev, double* out_score64_dev, int32_t* out_inexact_dev,
+                              uint8_t* out_flags_dev, void* block_dev, void* stream) {
+    if (!h || !x) return fail(PILOTT_EINVAL, "handle is NULL");
+    if (!x->connected) return fail(PILOTT_EINVAL, "exchange is not connected");
+    if (x->device != h->device) return fail(PILOTT_EINVAL, "store and exchange live on different devices");
+    if (nq < 1 || step < 0) return fail(PILOTT_EINVAL, "nq must be >= 1 and step >= 0 (every rank takes part in every step)");
+    if (2 * nq * k * 8 > x->block_bytes) return fail(PILOTT_EINVAL, "[2, nq, k] block exceeds block_bytes");
+    if (!q_dev || !out_idx_dev || !out_score_dev || !block_dev) return fail(PILOTT_EINVAL, "NULL query, output or block pointer");
+    DeviceGuard g(h->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    int rc = order_device_call(h, st);
+    if (rc) return rc;
+    // local top-k of this rank's rows (global indices) into the caller's block: [0] indices, [1] fp64 score bits
+    int64_t* blk_idx = (int64_t*)block_dev;
+    double* blk_sc = (double*)block_dev + nq * k;
+    rc = pilott_xchg_wait_buffer(x, (int)(step & 7), stream);          // the copies of step - 8 have left the block
+    if (rc) return rc;
+    rc = search_core(h, q_dev, nq, k, min_prio, req_tagmask, now_us, blk_idx, out_score_dev, blk_sc, out_inexact_dev,
+                     out_flags_dev, st);
+    if (rc) return rc;
+    rc = note_device_call(h, st);
+    if (rc) return rc;
+    rc = pilott_xchg_publish_copy(x, block_dev, 2 * nq * k * 8, step, (int)(step & 7), stream);
+    if (rc) return rc;
+    return pilott_xchg_merge(x, step, nq, k, out_idx_dev, out_score_dev, out_score64_dev, stream);
+}
+
 int pilott_xchg_check(pilott_xchg_t* x) {
     if (!x) return fail(PILOTT_EINVAL, "NULL pointer");
     DeviceGuard g(x->device);

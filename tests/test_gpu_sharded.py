@@ -80,6 +80,26 @@ def _worker(rank, world, port, n, dim, nq, k, out, exchange):
         assert torch.equal(i0, want_i) and torch.equal(s0, want_s)
         assert torch.equal(i1.flip(0), want_i) and torch.equal(s1.flip(0), want_s)
     st.check_exchange()
+    if exchange == "copy":
+        # the one-call C entry point a non-Python host uses: search + publish by copy + merge on one stream
+        import ctypes as C
+        from pilottai_b200 import _lib
+        lib = _lib.load()
+        xs = st._exchange_for(nq, k)
+        stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        for rep in range(10):                           # more steps than the exchange has slots
+            blk = torch.empty((2, nq, k), dtype=torch.int64, device="cuda")
+            o_i = torch.empty((nq, k), dtype=torch.int64, device="cuda")
+            o_s = torch.empty((nq, k), dtype=torch.float32, device="cuda")
+            o_s64 = torch.empty((nq, k), dtype=torch.float64, device="cuda")
+            cnt = torch.zeros(1, dtype=torch.int32, device="cuda")
+            _lib.check(lib.pilott_mem_search_sharded(st.local._h, xs[0], xs[1], q.data_ptr(), nq, k, 1, 0, 1_000_000,
+                                                     o_i.data_ptr(), o_s.data_ptr(), o_s64.data_ptr(), cnt.data_ptr(),
+                                                     None, blk.data_ptr(), stream))
+            xs[1] += 1
+            torch.cuda.synchronize()
+            assert int(cnt.item()) == 0 and torch.equal(o_i, want_i) and torch.equal(o_s64, want_s)
+        st.check_exchange()
     # k > 32: every shard answers through the large-k path, the exchange and the merge are the same
     i64, _, s64, _ = st.search(q, 64, min_priority=1, now_us=1_000_000)
     torch.cuda.synchronize()
