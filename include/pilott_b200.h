@@ -238,9 +238,9 @@ int pilott_mem_export(pilott_mem_t* h, uint16_t* vec_bits_host, float* inv_norm_
  *   publish: block_dev = this rank's block (bytes <= block_bytes, multiple of 16), step >= 0.
  *   publish_copy: the same block and flag, written by the copy engines (cudaMemcpyAsync into each
  *            peer's buffer on a stream the exchange owns, ordered behind `stream`): no kernel, so
- *            no SM is taken from the scan of the next batch -- on B200 the pair scan needs all 72
- *            SM pairs a GPU has, and one CTA of a collective's kernel on the wrong SM delays one
- *            pair by the whole collective.  buffer_id (0..7) names the caller's block buffer: call
+ *            no SM is taken from the scan of the next batch (the pair scan fills 72 of a B200's 74
+ *            SM pairs, one CTA per SM: a collective's kernel that lands on one of them delays that
+ *            pair by the whole collective).  buffer_id (0..7) names the caller's block buffer: call
  *            pilott_xchg_wait_buffer(x, buffer_id, stream) before the next search overwrites it.
  *   merge  : waits for every rank's block of `step`, writes the global top-k like
  *            pilott_topk_merge_packed.  Per rank, up to three publishes may be enqueued ahead of

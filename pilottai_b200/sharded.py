@@ -12,9 +12,9 @@ Three exchanges:
   "copy" (default) -- pilott_xchg_publish_copy: the block and a flag are written into every peer's mapped
          receive buffer by the copy engines (cudaMemcpyAsync on a side stream), the merge kernel
          acquires the flags.  No kernel runs for the exchange, so nothing competes with the scan of
-         the next batch for SMs: on B200 the pair scan occupies all 72 SM pairs, and a single CTA
-         of a collective's kernel on the wrong SM holds one pair back for the length of the
-         collective.  Measured on 8 B200, 1 M x 768, 1024-query batches, 0.177 ms of local search
+         the next batch for SMs: the pair scan fills 72 of a B200's 74 SM pairs with one CTA per
+         SM, and a collective's kernel that lands on one of them holds that pair back for the
+         length of the collective.  Measured on 8 B200, 1 M x 768, 1024-query batches, 0.177 ms of local search
          per step: 0.194 ms per step with this exchange, 0.230 with the NCCL one below.
          If peer mapping fails on any rank, every rank falls back to "nccl".
   "nccl" -- one all_gather_into_tensor of the packed block on NCCL's own stream (a process group
@@ -80,8 +80,8 @@ class ShardedSemanticStore:
     def _small_nccl_group(world: int):
         """A process group of its own for the exchange, with NCCL held to one CTA.  The block
         exchanged per step is ~160 KB, so bandwidth does not matter -- where the collective's kernel
-        RUNS does: the scan of the next batch wants 72 SM pairs of the 74, and every SM an all-gather
-        with the default channel count takes from it delays a CTA pair by the whole all-gather
+        RUNS does: the scan of the next batch wants 72 SM pairs of the 74, and every pair an all-gather
+        with the default channel count takes from it is delayed by the whole all-gather
         (measured on 4 B200, 0.306 ms of local search per step: 0.358 ms per step with NCCL's default, 0.315 with one CTA).  PILOTT_NCCL_MAX_CTAS overrides (0 = default
         group, NCCL's own choice).  Collective: every rank constructs its store at the same point."""
         n = int(os.environ.get("PILOTT_NCCL_MAX_CTAS", "1"))
