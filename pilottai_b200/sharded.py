@@ -146,6 +146,9 @@ class ShardedSemanticStore:
         handle = C.create_string_buffer(IPC_HANDLE_BYTES)
         x = C.c_void_p()
         rc = lib.pilott_xchg_create(self.device, self.rank, self.world, 2 * nq * k * 8, C.byref(x), handle)
+        if os.environ.get("PILOTT_XCHG_FORCE_FAIL") == str(self.rank):     # test hook: this rank cannot map its peers
+            lib.pilott_xchg_destroy(x)
+            rc = -1
         gathered = [None] * self.world
         dist.all_gather_object(gathered, handle.raw if rc == 0 else None, group=self.group)
         ok = rc == 0 and all(h is not None for h in gathered)
