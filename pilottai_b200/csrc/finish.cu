@@ -484,7 +484,7 @@ finish_sel_kernel(const __grid_constant__ FinishArgs a) {
     __syncthreads();
     const int R = s_R;
 
-    // 3. rounds of 16 survivors: gather the rows, then thread (c, j) walks partial sum j of survivor c
+    // 3. rounds of SEL_ROWS survivors: gather the rows, then thread (c, j) walks partial sum j of survivor c
     const int c = tid >> 3, j = tid & 7;
     for (int r0 = 0; r0 < R; r0 += SEL_ROWS) {
         const int nr = R - r0 < SEL_ROWS ? R - r0 : SEL_ROWS;

@@ -209,8 +209,10 @@ class ShardedSemanticStore:
             if by_copy:
                 check(_lib.load().pilott_xchg_publish_copy(xs[0], ptr(b["mine"]), b["mine"].numel() * 8, step, slot % 8,
                                                            self.local._stream()))
-            else:
-                check(_lib.load().pilott_xchg_publish(xs[0], ptr(b["mine"]), b["mine"].numel() * 8, step, self.local._stream()))
+                # (no event of our own on the search stream: the merge stream waits for this slot's copies
+                #  instead, which are ordered behind the search; one record fewer between finish and prepare)
+                return b, ("copy", xs[0], step, q.shape[0], k, slot % 8)
+            check(_lib.load().pilott_xchg_publish(xs[0], ptr(b["mine"]), b["mine"].numel() * 8, step, self.local._stream()))
             b["begun"].record(torch.cuda.current_stream(self.device))
             return b, ("p2p", xs[0], step, q.shape[0], k)
         if self.world > 1:
@@ -231,10 +233,15 @@ class ShardedSemanticStore:
         main = torch.cuda.current_stream(self.device)
         if self._merge_stream is None:
             self._merge_stream = torch.cuda.Stream(device=self.device)
-        self._merge_stream.wait_event(b["begun"])        # recorded by search_begin behind its local search / publish
+        if isinstance(work, tuple) and work[0] == "copy":
+            # this rank's outgoing copies of the step are ordered behind its local search: waiting for them
+            # orders the merge behind both (and a rank never parks its wait kernel before its own block is out)
+            check(_lib.load().pilott_xchg_wait_buffer(work[1], work[5], C.c_void_p(self._merge_stream.cuda_stream)))
+        else:
+            self._merge_stream.wait_event(b["begun"])    # recorded by search_begin behind its local search / publish
         with torch.cuda.stream(self._merge_stream):
             if isinstance(work, tuple):                  # peer-memory exchange: the block is already on its way
-                _, x, step, nq, k = work
+                _, x, step, nq, k = work[:5]
                 check(_lib.load().pilott_xchg_merge(x, step, nq, k, ptr(b["m_idx"]), ptr(b["m_sc"]), ptr(b["m_sc64"]),
                                                     self.local._stream()))
             else:
