@@ -352,17 +352,17 @@ finish_kernel(const uint64_t* __restrict__ partials, int slots_alloc, int list_l
 //   * nothing is taken on trust: the best survivor that was NOT re-scored joins `bound`, and the
 //     gap check (bound + err < exact k-th) proves the cut like it proves every other drop -- a
 //     query it cannot prove is flagged and goes to the second-chance pass as before;
-//   * work is spread as thread = (survivor, partial sum): 16 survivors x the 8 interleaved partial
+//   * work is spread as thread = (survivor, partial sum): 14 survivors x the 8 interleaved partial
 //     sums of the stated rule per round of 128 threads, so a round costs ld/8 iterations of
 //     {LDS.64 query (pre-converted to fp64 once per CTA), LDS.U16 row, one F2F, two DFMA}; the
 //     query norm is accumulated once (survivor 0's threads), not once per survivor;
 //   * the list length is a template parameter (no integer divisions, a fraction of the code).
 // Scores and indices are bit-identical to finish_kernel's whenever the query is not flagged.
 // ---------------------------------------------------------------------------------------
-constexpr int SEL_ROWS = 16;              // survivors staged and re-scored per round
+constexpr int SEL_ROWS = 14;              // survivors staged and re-scored per round: 14 rows + the query keep a CTA under 32 KB, so 7 CTAs share an SM and 1024 queries are one wave
 
 template <int LL>
-__global__ void __launch_bounds__(FIN_WARPS * 32, 6)
+__global__ void __launch_bounds__(FIN_WARPS * 32, 7)
 finish_sel_kernel(const __grid_constant__ FinishArgs a) {
     extern __shared__ __align__(16) unsigned char s_dyn[];      // [ld] fp64 query | [ld] bf16 query | [SEL_ROWS][ld*2+16] rows
     __shared__ uint64_t s_pool[FIN_WARPS][32];
