@@ -54,12 +54,15 @@ BURST_SECONDS = 1.0            # a timed region shorter than this runs at burst 
 
 def _peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    if os.path.exists(path):
+    fb = {"burst": 1400.0, "sustained": 1400.0, "hbm": 6650.0, "src": "fallback (B200_PROFILING.md)"}
+    try:
         with open(path) as f:
             p = json.load(f)
-        return {"burst": float(p["bf16_tflops"]), "sustained": float(p["bf16_tflops_sustained"]),
-                "hbm": float(p["hbm_gbs"]), "src": "MEASURED_PEAKS.json"}
-    return {"burst": 1400.0, "sustained": 1400.0, "hbm": 6650.0, "src": "fallback (B200_PROFILING.md)"}
+        burst = float(p.get("bf16_tflops") or p.get("bf16_tflops_burst") or fb["burst"])
+        return {"burst": burst, "sustained": float(p.get("bf16_tflops_sustained") or burst),
+                "hbm": float(p.get("hbm_gbs") or fb["hbm"]), "src": "MEASURED_PEAKS.json"}
+    except (OSError, ValueError, TypeError):
+        return fb
 
 
 def _traffic(rows, dim, world):
