@@ -74,7 +74,13 @@ class EnhancedMemory:
         self.coalesced_batches = 0                       # device batches the drain task has sent (bookkeeping for tests)
         self.max_size = int(max_size)
         self.dim = int(dim)
-        self._items: deque = deque(maxlen=self.max_size)       # MemoryItem, oldest first
+        # MemoryItems by insertion sequence number: item of sequence s sits at _ring[s % max_size] (the
+        # reference keeps a deque(maxlen) and only ever iterates it, :27; here every search result is an
+        # index lookup, and a deque of a million items is O(n) to index).  _total mirrors the device's
+        # count of rows ever appended, _count the rows held.
+        self._ring: List[Optional[MemoryItem]] = []
+        self._total = 0
+        self._count = 0
         self._store = SemanticStore(self.dim, self.max_size, device)
         self._embed = embedder or HashEmbedder(self.dim)
         self._tag_bits: Dict[str, int] = {}
@@ -170,13 +176,26 @@ class EnhancedMemory:
                 hi = min(n, lo + self.max_size)
                 s = await asyncio.to_thread(self._store.append, emb[lo:hi], prio[lo:hi], mask[lo:hi], exp[lo:hi])
                 first = s if first < 0 else first
-                self._items.extend(items[lo:hi])
+                for it in items[lo:hi]:
+                    slot = self._total % self.max_size
+                    if slot < len(self._ring):
+                        self._ring[slot] = it
+                    else:
+                        self._ring.append(it)
+                    self._total += 1
+                self._count = min(self._count + (hi - lo), self.max_size)
         return first
 
     # ---- search (reference :93-131) -------------------------------------------------------
     def _item_for_seq(self, seq: int) -> MemoryItem:
-        base = self._store.total - len(self._items)
-        return self._items[seq - base]
+        if not (self._total - self._count <= seq < self._total):
+            raise IndexError(f"sequence number {seq} is not held (rows {self._total - self._count}..{self._total - 1})")
+        return self._ring[seq % self.max_size]
+
+    @property
+    def _items(self) -> List[MemoryItem]:
+        """The held items, oldest first (what the reference's deque iterates)."""
+        return [self._ring[s % self.max_size] for s in range(self._total - self._count, self._total)]
 
     async def _device_search(self, q: np.ndarray, k: int, req: int, min_priority: int):
         async with self._semantic_lock:
@@ -200,12 +219,12 @@ class EnhancedMemory:
         todo = np.arange(q.shape[0])
         kk = max(4 * k, 64)
         while todo.size:
-            kk = min(kk, max(len(self._items), 1))
+            kk = min(kk, max(self._count, 1))
             idx, sc = await self._device_search(q[todo], kk, req, min_priority)
             again = []
             for r, qi in enumerate(todo):
                 keep = [j for j in range(kk) if idx[r, j] >= 0 and want <= self._item_for_seq(int(idx[r, j])).tags]
-                exhausted = kk >= len(self._items) or idx[r, kk - 1] < 0
+                exhausted = kk >= self._count or idx[r, kk - 1] < 0
                 if len(keep) >= k or exhausted:
                     keep = keep[:k]
                     out_i[qi, :len(keep)] = idx[r, keep]
@@ -334,7 +353,15 @@ class EnhancedMemory:
             async with self._semantic_lock, self._pattern_lock:
                 now = datetime.now()
                 kept, keep = await asyncio.to_thread(self._store.compact, _to_us(now))
-                self._items = deque((it for it, k in zip(self._items, keep) if k), maxlen=self.max_size)
+                # the device renumbers the survivors total - kept .. total - 1 in age order (pilott_mem_compact)
+                survivors = [it for it, k in zip(self._items, keep) if k]
+                self._count = len(survivors)
+                for i, it in enumerate(survivors):
+                    slot = (self._total - self._count + i) % self.max_size
+                    if slot < len(self._ring):
+                        self._ring[slot] = it
+                    else:                                  # (cannot happen: the ring only grows to max_size)
+                        self._ring.append(it)
                 for name in [n for n, p in self._pattern_store.items() if p["expires_at"] and now > p["expires_at"]]:
                     del self._pattern_store[name]
             self.last_cleanup = datetime.now()
@@ -342,7 +369,7 @@ class EnhancedMemory:
             raise ValueError(f"Cleanup failed: {str(e)}")
 
     def clear(self) -> None:
-        self._items.clear()
+        self._ring, self._total, self._count = [], 0, 0
         self._store.clear()
         self._tag_bits.clear()
         self._task_history.clear()
@@ -350,4 +377,4 @@ class EnhancedMemory:
         self._pattern_store.clear()
 
     def __len__(self) -> int:
-        return len(self._items)
+        return self._count
