@@ -330,14 +330,15 @@ def run_workload(name, args, ctx, full: bool):
             dist.all_reduce(n)
         return int(n.item())
 
-    def timed(nsteps: int, first: int, sample_clocks: bool, profile: bool):
+    def timed(nsteps: int, first: int, sample_clocks, profile: bool):
+        # sample_clocks: False, True (a sampler for this pass alone) or a running ClockSampler the caller stops
         # profile=True records CUDA events around every scan kernel, on its stream; an event between
         # two kernels also serialises them, which turns off the programmatic dependent launches the
         # step otherwise uses -- so throughput is taken from an un-profiled pass and the kernel time
         # from a profiled pass of the same steps.
         loc.set_profile(profile)
         launches0 = loc.launch_count()
-        sampler = ClockSampler(local).begin() if (sample_clocks and rank == 0) else None
+        sampler = ClockSampler(local).begin() if (sample_clocks is True and rank == 0) else None
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
         e0.record()
@@ -382,8 +383,14 @@ def run_workload(name, args, ctx, full: bool):
     drain()
     barrier()
     flagged_everywhere()
-    total_ms, _, launches, clocks = timed(args.steps, args.warmup, True, False)
-    prof_ms, kernel_ms, _, _ = timed(args.steps, args.warmup, False, True)
+    # one clock sampler over both passes (the same K steps twice): NVML answers in 1-20 ms on these
+    # boxes, so a 20 ms region alone can end up with a single sample
+    both = ClockSampler(local).begin() if rank == 0 else None
+    total_ms, _, launches, _ = timed(args.steps, args.warmup, both, False)
+    prof_ms, kernel_ms, _, _ = timed(args.steps, args.warmup, both, True)
+    clocks = both.stop() if both else None
+    if clocks:
+        clocks["covers"] = "the timed pass and the profiled pass of the same steps"
     if world > 1:
         store.check_exchange()
     n_flagged = flagged_everywhere()
