@@ -43,6 +43,9 @@ struct ScanArgs {
     int list_len;            // candidates per list the scan writes (16 or 32)
     int krank;               // rank of the first-tile list maxima used as cold-start threshold (16 or 32)
     int dbg;                 // developer switches for the tcgen05 kernel (0 in production)
+    uint32_t* progress;      // [units] tiles issued by each work unit (zeroed per search), or NULL: the groups of a
+                             // slot keep within `window` tiles of each other (long sweeps only)
+    int window;
     int collect_cap;         // > 0: second-chance pass (pair kernel): partials = uint32 [nq][collect_cap] ring slots,
                              // gthr = float-bit thresholds [nq], gmax = uint32 counters [nq]
 };

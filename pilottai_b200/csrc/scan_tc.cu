@@ -91,7 +91,8 @@ template <int CG, int KPT, bool COLLECT>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_c,
                const float* __restrict__ scale, const float* __restrict__ tile_max,
-               uint64_t* __restrict__ partials, uint32_t* __restrict__ gthr, uint32_t* __restrict__ gmax, int64_t nq, int64_t nslots, int64_t capacity, int64_t head, int kblocks, int slots, int slots_rem, int groups, int krank, int dbg_arg) {
+               uint64_t* __restrict__ partials, uint32_t* __restrict__ gthr, uint32_t* __restrict__ gmax,
+               uint32_t* __restrict__ progress, int window, int64_t nq, int64_t nslots, int64_t capacity, int64_t head, int kblocks, int slots, int slots_rem, int groups, int krank, int dbg_arg) {
     // Developer switches (profiling experiments, some of which give WRONG results on purpose) exist
     // only in -DPILOTT_DEBUG builds; in the production build `dbg` is the constant 0 and every
     // `dbg &` branch, counter and clock read below is compiled out.
@@ -185,6 +186,28 @@ scan_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
             int stage = 0; uint32_t phase = 0;
             for (int64_t t = t_lo; t < t_hi; ++t) {
                 const int n0 = (int)(t * BN) + (int)rank * Cfg::B_ROWS;
+                // Keep step with the other query groups that sweep this slot: a corpus tile is read from
+                // HBM once and served to the other groups from L2 only while they are within what L2
+                // holds of each other; over thousands of tiles they drift (10 M x 1024: the corpus came
+                // from DRAM twice per batch).  Before issuing tile i the producer waits until every
+                // group of the slot has issued tile i - window.  Only launched this way when the whole
+                // grid is resident (every unit it waits for is running); the wait is bounded anyway.
+                if (progress != nullptr) {
+                    const uint32_t ti = (uint32_t)(t - t_lo);
+                    if (leader) *reinterpret_cast<volatile uint32_t*>(progress + unit) = ti;
+                    if (ti > (uint32_t)window) {
+                        const uint32_t need = ti - (uint32_t)window;
+                        for (int spins = 0; spins < (1 << 16); ++spins) {
+                            uint32_t lo = 0xffffffffu;
+                            for (int g = 0; g < groups; ++g) {
+                                const uint32_t p = *reinterpret_cast<volatile uint32_t*>(progress + slot * groups + g);
+                                lo = p < lo ? p : lo;
+                            }
+                            if (lo >= need) break;
+                            __nanosleep(200);
+                        }
+                    }
+                }
                 for (int kb = 0; kb < kblocks; ++kb) {
                     mbar_wait(bar_empty + 8 * stage, phase ^ 1);
                     if (kb == 0) {
@@ -569,7 +592,7 @@ static cudaError_t launch_one(const ScanArgs& a, const CUtensorMap* map_q, const
     attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled();
     cfg.attrs = attr; cfg.numAttrs = 2;
     return cudaLaunchKernelEx(&cfg, scan_tc_kernel<CG, KPT, COLLECT>, *map_q, *map_c, a.scale, a.tile_max, a.partials, a.gthr, a.gmax,
-                              a.nq, a.nslots, a.capacity, a.head, kblocks, a.slots, a.slots_rem, groups,
+                              a.progress, a.window, a.nq, a.nslots, a.capacity, a.head, kblocks, a.slots, a.slots_rem, groups,
                               COLLECT ? a.collect_cap : a.krank, a.dbg);
 }
 
