@@ -350,14 +350,14 @@ int search_core(pilott_mem* h, const float* q_dev, int64_t nq, int k, int32_t mi
         a.partials = (uint64_t*)h->partials.p;
         a.gthr = (uint32_t*)h->gthr.p;
         a.gmax = a.gthr + nq32;
-        // Long sweeps: keep the query groups of a slot within a few tiles of each other, so that a corpus
-        // tile is read from HBM once (see scan_tc.cu).  Needs every unit resident at once (one wave).
+        // Experiment kept behind PILOTT_LOCKSTEP=n: keep the query groups of a slot within n tiles of each
+        // other, so that a corpus tile is read from HBM once on long sweeps (see scan_tc.cu).  Needs every
+        // unit resident at once (one wave).
         {
             const int groups_n = (int)((nq + 128 * cg - 1) / (128 * cg));
             const int units_n = groups_n * a.slots;
-            const int64_t tiles_per_slot = ((h->count + 255) / 256) / (a.slots > 0 ? a.slots : 1);
             static const int lockstep = [] { const char* e = getenv("PILOTT_LOCKSTEP"); return e ? atoi(e) : -1; }();
-            const bool want = lockstep >= 0 ? lockstep > 0 : tiles_per_slot >= 1024;   // measured: 10 M x 1024 +3.7 %, 1 M x 768 (217 tiles per slot) -9 %
+            const bool want = lockstep > 0;      // off unless PILOTT_LOCKSTEP=n asks for it: measured +1 % at 10 M x 1024, -4 % at 5 M, -9 % at 1 M
             if (want && groups_n > 1 && a.slots_rem == 0 && units_n * cg <= h->num_sms && (size_t)units_n <= n_prog) {
                 a.progress = a.gthr + nq32 + (size_t)nq * 32;
                 a.window = lockstep > 1 ? lockstep : 4;
