@@ -632,8 +632,13 @@ def run_ours(args):
     if not args.no_secondary:
         other = "10m" if args.workload == "1m" else "1m"
         t0 = time.perf_counter()
-        sec = run_workload(other, args, ctx, full=False)
-        sec["wall_s"] = time.perf_counter() - t0
+        try:
+            sec = run_workload(other, args, ctx, full=False)
+            sec["wall_s"] = time.perf_counter() - t0
+        except SystemExit:
+            raise
+        except Exception as e:                                      # secondary: never costs the headline line
+            sec = {"error": f"{type(e).__name__}: {e}"}
         secondary["retrieval_" + other] = sec
         if rank == 0 and world == 1:
             try:
